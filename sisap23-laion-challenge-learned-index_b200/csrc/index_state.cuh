@@ -1,0 +1,94 @@
+// index_state.cuh -- host-side state of one lmi_index (one CUDA device / one shard).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/lmi_b200.h"
+#include "common.cuh"
+#include "nav.cuh"
+#include "plan.cuh"
+
+namespace lmi {
+
+extern thread_local std::string g_last_error;
+int set_error(int code, const std::string& msg);
+
+#define LMI_CUDA(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess)                                                                     \
+      return lmi::set_error(LMI_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+  } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) { cudaFree(p); p = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace lmi
+
+struct lmi_index {
+  int device = 0;
+  int num_sms = 148;
+  int d_nav = 96, d = 768, C = 0;
+  cudaStream_t stream = nullptr;            // stream of the host-buffer entry points
+
+  // options
+  int rescore = LMI_RESCORE_TC;
+  int chunk_objects = 8192;
+  int kprime_extra = 6;
+  int timing = 1;
+  int rank = 0, world = 1, policy = LMI_SHARD_BUCKETS;
+
+  // model
+  lmi::NavLayers layers{};                  // device pointers inside
+  std::vector<void*> mlp_allocs;
+  bool has_mlp = false;
+
+  // store
+  bool store_open = false, has_store = false;
+  int64_t n_total = 0, n_local = 0, id_base = 1;
+  int64_t rows_seen = 0;
+  lmi::DevBuf cats, pos, block_hist, bucket_size, keep_lo, keep_hi, owner, bucket_ptr;   // build-time
+  lmi::DevBuf stage_rows;                                                                // host->device staging
+  uint16_t* x = nullptr;                    // [n_local, d] fp16, CSR by bucket
+  float* inv_norm = nullptr;                // [n_local]
+  uint32_t* ids = nullptr;                  // [n_local]
+  std::vector<int64_t> h_bucket_ptr;        // [C+1] local CSR (host copy)
+  std::vector<int64_t> h_chunks_sorted_prefix;   // prefix sums of chunks_b sorted descending
+  int64_t total_chunks = 0, max_chunks = 0;
+  CUtensorMap tmap_x{};                     // store tensor map (TC kernel)
+  bool tmap_x_ok = false;
+
+  // search workspace (grow-only)
+  lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;
+  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars;
+  lmi::DevBuf nav_cls, nav_probs, nav_x;
+  CUtensorMap tmap_q{};
+  void* tmap_q_ptr = nullptr; size_t tmap_q_rows = 0;
+  int64_t max_items = 0;
+
+  // stats
+  lmi::PlanScalars* h_scalars = nullptr;    // pinned
+  cudaEvent_t ev[5]{};
+  cudaStream_t last_stream = nullptr;
+  lmi_stats stats{};
+  bool stats_pending = false;
+  std::string rescore_name = "none";
+};

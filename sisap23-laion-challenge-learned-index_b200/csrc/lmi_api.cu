@@ -1,0 +1,175 @@
+// lmi_api.cu -- C-ABI of liblmi_b200.so (see include/lmi_b200.h).  Host orchestration only; the
+// kernels live in nav.cuh (K1), plan.cuh (K2), rescore_tc.cuh / rescore_simt.cuh (K3),
+// finalize.cuh (K4+K5) and store.cuh (bucket store build).
+#include "index_state.cuh"
+#include "store.cuh"
+#include "rescore_simt.cuh"
+#include "rescore_tc.cuh"
+#include "finalize.cuh"
+
+namespace lmi {
+
+thread_local std::string g_last_error;
+int set_error(int code, const std::string& msg) { g_last_error = msg; return code; }
+
+static int next_kprime(int need) {
+  for (int kp : {16, 32, 64, 128}) if (need <= kp) return kp;
+  return -1;
+}
+
+// cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D fp16 row-major [rows, d] tensor, box = [64 halves (128 B), box_rows], 128-byte swizzle
+static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)d * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kTcBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled failed, code " + std::to_string((int)r));
+  return LMI_OK;
+}
+
+}  // namespace lmi
+
+using namespace lmi;
+
+extern "C" {
+
+const char* lmi_last_error(void) { return g_last_error.c_str(); }
+const char* lmi_version(void) { return "lmi_b200 0.1.0 (sm_100a)"; }
+
+int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories) {
+  if (!out) return set_error(LMI_ERR_ARG, "out is NULL");
+  if (d_nav <= 0 || d_nav > 4096) return set_error(LMI_ERR_ARG, "d_nav out of range");
+  if (d <= 0 || d % 64 != 0 || d > 1024) return set_error(LMI_ERR_ARG, "d must be a multiple of 64, <= 1024");
+  if (n_categories <= 0 || n_categories > 65536) return set_error(LMI_ERR_ARG, "n_categories out of range");
+  int ndev = 0;
+  LMI_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return set_error(LMI_ERR_ARG, "no such CUDA device");
+  LMI_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  LMI_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return set_error(LMI_ERR_CUDA, std::string("lmi_b200 is built for sm_100a only; device is sm_") +
+                                       std::to_string(prop.major) + std::to_string(prop.minor));
+  lmi_index* idx = new lmi_index();
+  idx->device = device;
+  idx->num_sms = prop.multiProcessorCount;
+  idx->d_nav = d_nav; idx->d = d; idx->C = n_categories;
+  LMI_CUDA(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
+  for (auto& e : idx->ev) LMI_CUDA(cudaEventCreate(&e));
+  LMI_CUDA(cudaMallocHost(&idx->h_scalars, sizeof(PlanScalars)));
+  memset(idx->h_scalars, 0, sizeof(PlanScalars));
+  *out = idx;
+  return LMI_OK;
+}
+
+void lmi_destroy(lmi_index* idx) {
+  if (!idx) return;
+  cudaSetDevice(idx->device);
+  cudaDeviceSynchronize();
+  for (void* p : idx->mlp_allocs) cudaFree(p);
+  DevBuf* bufs[] = {&idx->cats, &idx->pos, &idx->block_hist, &idx->bucket_size, &idx->keep_lo, &idx->keep_hi,
+                    &idx->owner, &idx->bucket_ptr, &idx->stage_rows, &idx->ws_qnav, &idx->ws_q16, &idx->ws_out_d,
+                    &idx->ws_out_i, &idx->ws_thr, &idx->ws_cls64, &idx->top_cls, &idx->m_b, &idx->qoff,
+                    &idx->chunks_b, &idx->plist_base, &idx->slot_pair, &idx->pair_slot, &idx->items, &idx->plists,
+                    &idx->qg, &idx->scalars, &idx->nav_cls, &idx->nav_probs, &idx->nav_x};
+  for (DevBuf* b : bufs) b->release();
+  if (idx->x) cudaFree(idx->x);
+  if (idx->inv_norm) cudaFree(idx->inv_norm);
+  if (idx->ids) cudaFree(idx->ids);
+  if (idx->h_scalars) cudaFreeHost(idx->h_scalars);
+  for (auto& e : idx->ev) if (e) cudaEventDestroy(e);
+  if (idx->stream) cudaStreamDestroy(idx->stream);
+  delete idx;
+}
+
+int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
+  if (!idx || !name) return set_error(LMI_ERR_ARG, "NULL argument");
+  std::string n(name);
+  if (n == "rescore") {
+    if (value != LMI_RESCORE_SIMT && value != LMI_RESCORE_TC) return set_error(LMI_ERR_ARG, "rescore: 0 (simt) or 1 (tc)");
+    idx->rescore = (int)value;
+  } else if (n == "chunk_objects") {
+    if (value < 256 || value > (1 << 24)) return set_error(LMI_ERR_ARG, "chunk_objects out of range");
+    if (idx->has_store || idx->store_open) return set_error(LMI_ERR_STATE, "chunk_objects must be set before the store is built");
+    idx->chunk_objects = (int)((value + 255) / 256 * 256);
+  } else if (n == "kprime_extra") {
+    if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
+    idx->kprime_extra = (int)value;
+  } else if (n == "timing") {
+    idx->timing = value ? 1 : 0;
+  } else {
+    return set_error(LMI_ERR_ARG, "unknown option " + n);
+  }
+  return LMI_OK;
+}
+
+int lmi_set_shard(lmi_index* idx, int rank, int world, int policy) {
+  if (!idx) return set_error(LMI_ERR_ARG, "NULL index");
+  if (world < 1 || rank < 0 || rank >= world) return set_error(LMI_ERR_ARG, "bad rank/world");
+  if (policy != LMI_SHARD_BUCKETS && policy != LMI_SHARD_STRIPES) return set_error(LMI_ERR_ARG, "bad shard policy");
+  if (idx->has_store || idx->store_open) return set_error(LMI_ERR_STATE, "set the shard before building the store");
+  idx->rank = rank; idx->world = world; idx->policy = policy;
+  return LMI_OK;
+}
+
+int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const float* const* W, const float* const* b) {
+  if (!idx || !out_dims || !W || !b) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (n_layers < 1 || n_layers > kNavMaxLayers) return set_error(LMI_ERR_ARG, "1..8 linear layers supported");
+  if (out_dims[n_layers - 1] != idx->C) return set_error(LMI_ERR_ARG, "last layer width must equal n_categories");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  for (void* p : idx->mlp_allocs) cudaFree(p);
+  idx->mlp_allocs.clear();
+  NavLayers L{};
+  L.n_layers = n_layers;
+  L.max_width = idx->d_nav;
+  int in = idx->d_nav;
+  for (int l = 0; l < n_layers; ++l) {
+    const int out = out_dims[l];
+    if (out <= 0 || out > 65536) return set_error(LMI_ERR_ARG, "layer width out of range");
+    L.in_dim[l] = in; L.out_dim[l] = out;
+    L.max_width = std::max(L.max_width, out);
+    std::vector<float> wt((size_t)in * out);            // transpose nn.Linear.weight [out,in] -> [in,out]
+    for (int o = 0; o < out; ++o)
+      for (int i = 0; i < in; ++i) wt[(size_t)i * out + o] = W[l][(size_t)o * in + i];
+    float *dw = nullptr, *db = nullptr;
+    LMI_CUDA(cudaMalloc(&dw, wt.size() * sizeof(float)));
+    idx->mlp_allocs.push_back(dw);
+    LMI_CUDA(cudaMalloc(&db, (size_t)out * sizeof(float)));
+    idx->mlp_allocs.push_back(db);
+    LMI_CUDA(cudaMemcpy(dw, wt.data(), wt.size() * sizeof(float), cudaMemcpyHostToDevice));
+    LMI_CUDA(cudaMemcpy(db, b[l], (size_t)out * sizeof(float), cudaMemcpyHostToDevice));
+    L.wt[l] = dw; L.bias[l] = db;
+    in = out;
+  }
+  if (nav_smem_bytes(L) > 200 * 1024) return set_error(LMI_ERR_ARG, "MLP too wide for the navigation kernel (max width 800)");
+  idx->layers = L;
+  idx->has_mlp = true;
+  LMI_CUDA(cudaFuncSetAttribute(nav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nav_smem_bytes(L)));
+  return LMI_OK;
+}
+
+}  // extern "C"
+
+#include "lmi_api_store.inl"
+#include "lmi_api_search.inl"

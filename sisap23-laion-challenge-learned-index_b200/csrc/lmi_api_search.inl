@@ -1,0 +1,288 @@
+// lmi_api_search.inl -- navigation + search pipeline (included by lmi_api.cu)
+
+namespace lmi {
+
+static int launch_nav(lmi_index* idx, const float* x_dev, int64_t n, int n_top, int32_t* cls_dev, float* probs_dev,
+                      cudaStream_t st) {
+  if (n <= 0) return LMI_OK;
+  const int64_t grid = (n + kNavTQ - 1) / kNavTQ;
+  nav_kernel<<<(unsigned)grid, kNavThreads, nav_smem_bytes(idx->layers), st>>>(x_dev, n, idx->layers, n_top, cls_dev, probs_dev);
+  LMI_CUDA(cudaGetLastError());
+  return LMI_OK;
+}
+
+template <int KP>
+static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaStream_t st) {
+  const int d = idx->d;
+  bool done = false;
+  if constexpr (KP <= 64) {
+   if (idx->rescore == LMI_RESCORE_TC) {
+    done = true;
+    constexpr int STAGES = (KP <= 16) ? 4 : 3;
+    auto kern = rescore_tc_kernel<KP, STAGES>;
+    constexpr size_t smem = tc_smem_bytes<KP, STAGES>();
+    static bool attr_done = false;
+    if (!attr_done) {
+      LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_done = true;
+    }
+    kern<<<idx->num_sms, kTcThreads, smem, st>>>(idx->tmap_q, idx->tmap_x, d, idx->inv_norm, idx->items.as<WorkItem>(),
+                                                 idx->scalars.as<PlanScalars>(), idx->plists.as<Cand>());
+    idx->rescore_name = "rescore_tc_kernel";
+   }
+  }
+  if (!done) {
+    auto kern = rescore_simt_kernel<KP>;
+    constexpr size_t smem = simt_smem_bytes<KP>();
+    static bool attr_done = false;
+    if (!attr_done) {
+      LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_done = true;
+    }
+    kern<<<idx->num_sms * 2, kTileQ, smem, st>>>(q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->x, idx->inv_norm,
+                                                 idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
+                                                 idx->plists.as<Cand>());
+    idx->rescore_name = "rescore_simt_kernel";
+  }
+  LMI_CUDA(cudaGetLastError());
+  return LMI_OK;
+}
+
+// The whole hot path on `st`.  Exactly one of q_nav_dev / cls64_dev is used to obtain the bucket
+// list: navigation (search) or caller-supplied categories (search_rank, nb = 1).
+static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls64_dev, const uint16_t* q16_dev,
+                      int64_t nq, int nb, int k, const double* thr_dev, int mode, double* out_d, uint32_t* out_i,
+                      Partial* out_p, cudaStream_t st) {
+  if (!idx->has_store) return set_error(LMI_ERR_STATE, "bucket store not built (lmi_store_* / lmi_set_buckets)");
+  if (q_nav_dev && !idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");   // LearnedIndex.py:60
+  if (nq <= 0 || nq > (1 << 24)) return set_error(LMI_ERR_ARG, "nq out of range");
+  if (nb < 1 || nb > idx->C) return set_error(LMI_ERR_ARG, "n_buckets must be in [1, n_categories]");
+  if (k < 1) return set_error(LMI_ERR_ARG, "k must be >= 1");
+  const int KP = next_kprime(k + idx->kprime_extra);
+  if (KP < 0) return set_error(LMI_ERR_ARG, "k too large (k + kprime_extra <= 128)");
+  if (nq * nb >= (1LL << 31)) return set_error(LMI_ERR_ARG, "nq * n_buckets too large");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  const int C = idx->C, d = idx->d;
+  const int64_t n_pairs = nq * nb;
+
+  // ---- workspace ----
+  LMI_CUDA(idx->top_cls.reserve((size_t)n_pairs * 4));
+  LMI_CUDA(idx->m_b.reserve((size_t)C * 4));
+  LMI_CUDA(idx->qoff.reserve((size_t)(C + 1) * 4));
+  LMI_CUDA(idx->chunks_b.reserve((size_t)C * 4));
+  LMI_CUDA(idx->plist_base.reserve((size_t)C * 8));
+  LMI_CUDA(idx->slot_pair.reserve((size_t)n_pairs * 4));
+  LMI_CUDA(idx->pair_slot.reserve((size_t)n_pairs * 4));
+  LMI_CUDA(idx->scalars.reserve(sizeof(PlanScalars)));
+  const int64_t qtiles_max = (nq + kTileQ - 1) / kTileQ;
+  const int64_t items_a = qtiles_max * idx->total_chunks;
+  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(idx->max_chunks, 1);
+  const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
+  if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
+  LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
+  const int64_t max_plists = std::max<int64_t>(1, nq * idx->h_chunks_sorted_prefix[std::min(nb, C)]);
+  LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
+  const bool use_tc = (idx->rescore == LMI_RESCORE_TC && KP <= 64);
+  if (use_tc) {
+    if (!idx->tmap_x_ok) return set_error(LMI_ERR_STATE, "store tensor map missing (empty shard?)");
+    // +128 rows of slack: the last tile's TMA box may start up to 127 rows before the end
+    LMI_CUDA(idx->qg.reserve((size_t)(n_pairs + kTileQ) * d * 2));
+    const size_t rows_cap = idx->qg.cap / ((size_t)d * 2);
+    if (idx->tmap_q_ptr != idx->qg.p || idx->tmap_q_rows != rows_cap) {
+      int rc = make_tmap(&idx->tmap_q, idx->qg.p, rows_cap, d, kTileQ);
+      if (rc != LMI_OK) return rc;
+      idx->tmap_q_ptr = idx->qg.p; idx->tmap_q_rows = rows_cap;
+    }
+  }
+
+  const bool timing = idx->timing != 0;
+  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[0], st));
+  // ---- K1 navigation ----
+  int32_t* top = idx->top_cls.as<int32_t>();
+  if (q_nav_dev) {
+    int rc = launch_nav(idx, q_nav_dev, nq, nb, top, nullptr, st);
+    if (rc != LMI_OK) return rc;
+  } else {
+    cast_i64_to_i32_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(cls64_dev, n_pairs, top);
+  }
+  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[1], st));
+  // ---- K2 plan ----
+  LMI_CUDA(cudaMemsetAsync(idx->m_b.p, 0, (size_t)C * 4, st));
+  plan_count_kernel<<<idx->num_sms * 2, 256, 0, st>>>(top, n_pairs, C, idx->m_b.as<int32_t>());
+  plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, idx->chunk_objects,
+                                        idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
+                                        idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>());
+  plan_scatter_kernel<<<C, 256, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
+                                         idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
+  plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());
+  if (use_tc)   // A operand of the tensor-core GEMM: query rows in bucket order
+    gather_queries_kernel<<<idx->num_sms * 4, 256, 0, st>>>(q16_dev, idx->slot_pair.as<int32_t>(),
+                                                            idx->scalars.as<PlanScalars>(), nb, d, idx->qg.as<uint16_t>());
+  LMI_CUDA(cudaGetLastError());
+  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[2], st));
+  // ---- K3 rescoring ----
+  int rc = LMI_OK;
+  switch (KP) {
+    case 16: rc = launch_rescore<16>(idx, q16_dev, nb, st); break;
+    case 32: rc = launch_rescore<32>(idx, q16_dev, nb, st); break;
+    case 64: rc = launch_rescore<64>(idx, q16_dev, nb, st); break;
+    default: rc = launch_rescore<128>(idx, q16_dev, nb, st); break;
+  }
+  if (rc != LMI_OK) return rc;
+  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[3], st));
+  // ---- K4 + K5 finalize ----
+  finalize_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, st>>>(
+      nq, nb, k, KP, d, top, idx->pair_slot.as<int32_t>(), idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(),
+      idx->plist_base.as<int64_t>(), idx->plists.as<Cand>(), q16_dev, idx->x, idx->ids, thr_dev,
+      idx->scalars.as<PlanScalars>(), mode, out_d, out_i, out_p);
+  LMI_CUDA(cudaGetLastError());
+  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[4], st));
+  LMI_CUDA(cudaMemcpyAsync(idx->h_scalars, idx->scalars.p, sizeof(PlanScalars), cudaMemcpyDeviceToHost, st));
+  idx->stats.nq = (int32_t)nq; idx->stats.n_buckets = nb; idx->stats.k = k; idx->stats.kprime = KP;
+  idx->stats.n_objects_local = idx->n_local;
+  idx->last_stream = st;
+  idx->stats_pending = true;
+  return LMI_OK;
+}
+
+}  // namespace lmi
+
+extern "C" {
+
+int lmi_navigate(lmi_index* idx, const float* q_nav, int64_t nq, int n_top, int64_t* out_classes, float* out_probs) {
+  if (!idx || !q_nav || !out_classes) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (!idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");
+  if (n_top < 1 || n_top > idx->C) return set_error(LMI_ERR_ARG, "n_top must be in [1, n_categories]");
+  if (nq < 0) return set_error(LMI_ERR_ARG, "nq < 0");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  cudaStream_t st = idx->stream;
+  const int64_t step = 1 << 20;
+  std::vector<int32_t> h_cls;
+  for (int64_t lo = 0; lo < nq; lo += step) {
+    const int64_t cnt = std::min(step, nq - lo);
+    LMI_CUDA(idx->nav_x.reserve((size_t)cnt * idx->d_nav * 4));
+    LMI_CUDA(idx->nav_cls.reserve((size_t)cnt * n_top * 4));
+    if (out_probs) LMI_CUDA(idx->nav_probs.reserve((size_t)cnt * n_top * 4));
+    LMI_CUDA(cudaMemcpyAsync(idx->nav_x.p, q_nav + (size_t)lo * idx->d_nav, (size_t)cnt * idx->d_nav * 4, cudaMemcpyHostToDevice, st));
+    int rc = launch_nav(idx, idx->nav_x.as<float>(), cnt, n_top, idx->nav_cls.as<int32_t>(),
+                        out_probs ? idx->nav_probs.as<float>() : nullptr, st);
+    if (rc != LMI_OK) return rc;
+    h_cls.resize((size_t)cnt * n_top);
+    LMI_CUDA(cudaMemcpyAsync(h_cls.data(), idx->nav_cls.p, h_cls.size() * 4, cudaMemcpyDeviceToHost, st));
+    if (out_probs)
+      LMI_CUDA(cudaMemcpyAsync(out_probs + (size_t)lo * n_top, idx->nav_probs.p, (size_t)cnt * n_top * 4, cudaMemcpyDeviceToHost, st));
+    LMI_CUDA(cudaStreamSynchronize(st));
+    for (size_t i = 0; i < h_cls.size(); ++i) out_classes[(size_t)lo * n_top + i] = h_cls[i];
+  }
+  return LMI_OK;
+}
+
+int lmi_predict(lmi_index* idx, const float* x_nav, int64_t n, int64_t* out_category) {
+  return lmi_navigate(idx, x_nav, n, 1, out_category, nullptr);
+}
+
+int lmi_search_device(lmi_index* idx, const float* q_nav_dev, const uint16_t* q_f16_dev, int64_t nq, int n_buckets, int k,
+                      double* out_dists_dev, uint32_t* out_ids_dev, void* stream) {
+  if (!idx || !q_nav_dev || !q_f16_dev || !out_dists_dev || !out_ids_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  return run_search(idx, q_nav_dev, nullptr, q_f16_dev, nq, n_buckets, k, nullptr, 0, out_dists_dev, out_ids_dev, nullptr,
+                    reinterpret_cast<cudaStream_t>(stream));
+}
+
+int lmi_search(lmi_index* idx, const float* q_nav, const uint16_t* q_f16, int64_t nq, int n_buckets, int k,
+               double* out_dists, uint32_t* out_ids) {
+  if (!idx || !q_nav || !q_f16 || !out_dists || !out_ids) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (nq <= 0) return set_error(LMI_ERR_ARG, "nq must be positive");
+  if (k < 1) return set_error(LMI_ERR_ARG, "k must be >= 1");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  cudaStream_t st = idx->stream;
+  LMI_CUDA(idx->ws_qnav.reserve((size_t)nq * idx->d_nav * 4));
+  LMI_CUDA(idx->ws_q16.reserve((size_t)nq * idx->d * 2));
+  LMI_CUDA(idx->ws_out_d.reserve((size_t)nq * k * 8));
+  LMI_CUDA(idx->ws_out_i.reserve((size_t)nq * k * 4));
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_qnav.p, q_nav, (size_t)nq * idx->d_nav * 4, cudaMemcpyHostToDevice, st));
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, q_f16, (size_t)nq * idx->d * 2, cudaMemcpyHostToDevice, st));
+  int rc = run_search(idx, idx->ws_qnav.as<float>(), nullptr, idx->ws_q16.as<uint16_t>(), nq, n_buckets, k, nullptr, 0,
+                      idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st);
+  if (rc != LMI_OK) return rc;
+  LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaStreamSynchronize(st));
+  return LMI_OK;
+}
+
+int lmi_search_rank(lmi_index* idx, const uint16_t* q_f16, int64_t nq, const int64_t* category_per_query, int k,
+                    const double* threshold, double* out_dists, uint32_t* out_ids) {
+  if (!idx || !q_f16 || !category_per_query || !out_dists || !out_ids) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (nq <= 0) return set_error(LMI_ERR_ARG, "nq must be positive");
+  if (k < 1) return set_error(LMI_ERR_ARG, "k must be >= 1");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  cudaStream_t st = idx->stream;
+  LMI_CUDA(idx->ws_cls64.reserve((size_t)nq * 8));
+  LMI_CUDA(idx->ws_q16.reserve((size_t)nq * idx->d * 2));
+  LMI_CUDA(idx->ws_out_d.reserve((size_t)nq * k * 8));
+  LMI_CUDA(idx->ws_out_i.reserve((size_t)nq * k * 4));
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_cls64.p, category_per_query, (size_t)nq * 8, cudaMemcpyHostToDevice, st));
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, q_f16, (size_t)nq * idx->d * 2, cudaMemcpyHostToDevice, st));
+  const double* thr_dev = nullptr;
+  if (threshold) {
+    LMI_CUDA(idx->ws_thr.reserve((size_t)nq * 8));
+    LMI_CUDA(cudaMemcpyAsync(idx->ws_thr.p, threshold, (size_t)nq * 8, cudaMemcpyHostToDevice, st));
+    thr_dev = idx->ws_thr.as<double>();
+  }
+  int rc = run_search(idx, nullptr, idx->ws_cls64.as<int64_t>(), idx->ws_q16.as<uint16_t>(), nq, 1, k, thr_dev, 0,
+                      idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st);
+  if (rc != LMI_OK) return rc;
+  LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaStreamSynchronize(st));
+  return LMI_OK;
+}
+
+int64_t lmi_partial_bytes(int64_t nq, int k) { return nq * (int64_t)k * (int64_t)sizeof(Partial); }
+
+int lmi_search_partial_device(lmi_index* idx, const float* q_nav_dev, const uint16_t* q_f16_dev, int64_t nq, int n_buckets,
+                              int k, void* partial_dev, void* stream) {
+  if (!idx || !q_nav_dev || !q_f16_dev || !partial_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  return run_search(idx, q_nav_dev, nullptr, q_f16_dev, nq, n_buckets, k, nullptr, 1, nullptr, nullptr,
+                    reinterpret_cast<Partial*>(partial_dev), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int lmi_merge_partials_device(lmi_index* idx, const void* gathered_dev, int world, int64_t nq, int k, double* out_dists_dev,
+                              uint32_t* out_ids_dev, void* stream) {
+  if (!idx || !gathered_dev || !out_dists_dev || !out_ids_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (world < 1 || nq <= 0 || k < 1) return set_error(LMI_ERR_ARG, "bad world/nq/k");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  merge_partials_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const Partial*>(gathered_dev), world, nq, k, out_dists_dev, out_ids_dev);
+  LMI_CUDA(cudaGetLastError());
+  return LMI_OK;
+}
+
+int lmi_get_stats(lmi_index* idx, lmi_stats* out) {
+  if (!idx || !out) return set_error(LMI_ERR_ARG, "NULL argument");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  if (idx->stats_pending) {
+    LMI_CUDA(cudaStreamSynchronize(idx->last_stream));
+    const PlanScalars& s = *idx->h_scalars;
+    idx->stats.n_work_items = s.n_items;
+    idx->stats.pairs = s.pairs;
+    idx->stats.bucket_bytes = s.bucket_objs * idx->d * 2;
+    idx->stats.n_partial_lists = s.n_plists;
+    idx->stats.n_uncertified = (int64_t)s.n_uncertified;
+    double e; unsigned long long bits = s.max_err_bits; memcpy(&e, &bits, 8);
+    idx->stats.max_abs_score_err = e;
+    if (idx->timing) {
+      float ms[4] = {0, 0, 0, 0};
+      for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&ms[i], idx->ev[i], idx->ev[i + 1]);
+      idx->stats.ms_navigate = ms[0]; idx->stats.ms_plan = ms[1]; idx->stats.ms_rescore = ms[2]; idx->stats.ms_finalize = ms[3];
+      cudaEventElapsedTime(&idx->stats.ms_total, idx->ev[0], idx->ev[4]);
+    }
+    idx->stats_pending = false;
+  }
+  *out = idx->stats;
+  return LMI_OK;
+}
+
+const char* lmi_rescore_kernel_name(lmi_index* idx) { return idx ? idx->rescore_name.c_str() : ""; }
+
+}  // extern "C"

@@ -1,0 +1,193 @@
+// plan.cuh -- K2: invert per-query bucket lists into per-bucket query lists and build the
+// rescoring work list, entirely on the device (no host round trip inside a search).
+//
+// Replaces the scan ``cat_idxs = np.where(pred_categories == cat)`` that the reference repeats
+// for every (rank, category) (search/li/LearnedIndex.py:143-144): one counting sort of the
+// nq*nb (query, rank) pairs by bucket.  The order inside a bucket is ascending (query, rank),
+// so the layout -- and with it every downstream tie-break -- is deterministic.
+#pragma once
+#include "common.cuh"
+
+namespace lmi {
+
+struct PlanScalars {          // device-resident scalars of one search
+  int32_t n_items;            // work items
+  int32_t n_slots;            // = sum_b m_b (pairs whose bucket is non-empty on this shard may be fewer)
+  int64_t n_plists;           // partial lists
+  int64_t pairs;              // sum_b m_b * n_b
+  int64_t bucket_objs;        // sum_{b: m_b>0} n_b
+  unsigned long long n_uncertified;
+  unsigned long long max_err_bits;   // float64 bits of max |cos32-cos64| (atomicMax on non-negative doubles)
+  int32_t work_counter;       // dynamic scheduler cursor
+  int32_t pad;
+};
+
+// m_b histogram.  top_cls: int32 [nq*nb]; entries outside [0,C) are ignored.
+__global__ void plan_count_kernel(const int32_t* __restrict__ top_cls, int64_t n_pairs, int C,
+                                  int32_t* __restrict__ m_b) {
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < n_pairs;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int c = top_cls[e];
+    if (c >= 0 && c < C) atomicAdd(&m_b[c], 1);
+  }
+}
+
+// Single CTA: prefix sums over buckets + work item expansion.
+//   bucket_ptr: int64 [C+1] CSR of the local store;  chunk: objects per work item.
+//   outputs: qoff int32 [C+1]; chunks_b int32 [C]; plist_base int64 [C]; items; scalars.
+__global__ void __launch_bounds__(1024)
+plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ bucket_ptr, int C,
+                  int chunk, int32_t* __restrict__ qoff, int32_t* __restrict__ chunks_b,
+                  int64_t* __restrict__ plist_base, WorkItem* __restrict__ items, int max_items,
+                  PlanScalars* __restrict__ sc) {
+  __shared__ long long s_scan[1024];
+  __shared__ long long s_carry[3];
+  const int tid = threadIdx.x;
+  if (tid < 3) s_carry[tid] = 0;
+  long long tot_pairs = 0, tot_objs = 0;
+  __syncthreads();
+  // three running exclusive scans, processed in blocks of 1024 buckets:
+  //   0: slots (m_b)   1: items (qtiles*chunks)   2: plists (m_b*chunks)
+  for (int base = 0; base < C; base += 1024) {
+    const int b = base + tid;
+    long long m = 0, nobj = 0, ch = 0, qt = 0;
+    if (b < C) {
+      nobj = bucket_ptr[b + 1] - bucket_ptr[b];
+      m = (nobj > 0) ? m_b[b] : 0;                 // empty bucket: contributes nothing (LearnedIndex.py:147)
+      ch = (nobj + chunk - 1) / chunk;
+      qt = (m + kTileQ - 1) / kTileQ;
+      chunks_b[b] = (int)ch;
+      tot_pairs += m * nobj;
+      if (m > 0) tot_objs += nobj;
+    }
+    long long vals[3] = {m, qt * ch, m * ch};
+    long long excl[3];
+    for (int w = 0; w < 3; ++w) {
+      s_scan[tid] = vals[w];
+      __syncthreads();
+      for (int off = 1; off < 1024; off <<= 1) {
+        long long t = (tid >= off) ? s_scan[tid - off] : 0;
+        __syncthreads();
+        s_scan[tid] += t;
+        __syncthreads();
+      }
+      excl[w] = s_carry[w] + s_scan[tid] - vals[w];
+      __syncthreads();
+      if (tid == 1023) s_carry[w] += s_scan[1023];
+      __syncthreads();
+    }
+    if (b < C) {
+      qoff[b] = (int)excl[0];
+      plist_base[b] = excl[2];
+      const long long obj0 = bucket_ptr[b];
+      long long it = excl[1];
+      // query tile innermost: consecutive items (-> CTAs running at the same time) share an
+      // object chunk, so it is fetched from HBM once and re-read from L2 by the other tiles.
+      for (int c = 0; c < ch; ++c) {
+        for (int t = 0; t < qt; ++t, ++it) {
+          if (it >= max_items) continue;
+          WorkItem wi;
+          wi.slot_base = (int)excl[0] + t * kTileQ;
+          wi.rows = (int)min((long long)kTileQ, m - (long long)t * kTileQ);
+          wi.obj_begin = (int)(obj0 + (long long)c * chunk);
+          wi.obj_count = (int)min((long long)chunk, nobj - (long long)c * chunk);
+          wi.plist_base = excl[2] + (long long)t * kTileQ * ch + c;
+          wi.plist_stride = (int)ch;
+          wi.bucket = b;
+          items[it] = wi;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // reduce the two totals
+  s_scan[tid] = tot_pairs;
+  __syncthreads();
+  for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
+  const long long pairs = s_scan[0];
+  __syncthreads();
+  s_scan[tid] = tot_objs;
+  __syncthreads();
+  for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
+  if (tid == 0) {
+    qoff[C] = (int)s_carry[0];
+    sc->n_slots = (int)s_carry[0];
+    sc->n_items = (int)min((long long)max_items, s_carry[1]);
+    sc->n_plists = s_carry[2];
+    sc->pairs = pairs;
+    sc->bucket_objs = s_scan[0];
+    sc->n_uncertified = 0ull;
+    sc->max_err_bits = 0ull;
+    sc->work_counter = 0;
+  }
+}
+
+// One CTA per bucket: ordered compaction of the (query, rank) pairs routed to it.
+//   slot_pair int32 [n_slots]: pair index e = q*nb + r of every slot (bucket-major, e ascending)
+//   pair_slot int32 [nq*nb]  : slot of every pair, -1 if its bucket is empty / out of range
+__global__ void __launch_bounds__(256)
+plan_scatter_kernel(const int32_t* __restrict__ top_cls, int64_t n_pairs, int C,
+                    const int32_t* __restrict__ qoff, const int64_t* __restrict__ bucket_ptr,
+                    int32_t* __restrict__ slot_pair, int32_t* __restrict__ pair_slot) {
+  const int b = blockIdx.x;
+  __shared__ int s_warp[8];
+  __shared__ int s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool live = (bucket_ptr[b + 1] - bucket_ptr[b]) > 0;
+  if (tid == 0) s_base = qoff[b];
+  __syncthreads();
+  for (int64_t e0 = 0; e0 < n_pairs; e0 += 256) {
+    const int64_t e = e0 + tid;
+    const int c = (e < n_pairs) ? top_cls[e] : -1;
+    const bool mine = (c == b);
+    const unsigned bal = __ballot_sync(0xffffffffu, mine);
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { const int v = s_warp[w]; if (w < warp) before += v; total += v; }
+    if (mine) {
+      if (live) {
+        const int slot = s_base + before + __popc(bal & ((1u << lane) - 1u));
+        slot_pair[slot] = (int)e;
+        pair_slot[e] = slot;
+      } else {
+        pair_slot[e] = -1;
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && live) s_base += total;
+    __syncthreads();
+  }
+}
+
+// pairs whose class id is outside [0,C) never match a bucket CTA: mark them explicitly.
+__global__ void plan_mark_invalid_kernel(const int32_t* __restrict__ top_cls, int64_t n_pairs, int C,
+                                         int32_t* __restrict__ pair_slot) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e < n_pairs) { const int c = top_cls[e]; if (c < 0 || c >= C) pair_slot[e] = -1; }
+}
+
+// caller-supplied categories (search_single path): int64 -> int32, anything unrepresentable -> -1
+__global__ void cast_i64_to_i32_kernel(const int64_t* __restrict__ in, int64_t n, int32_t* __restrict__ out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) { const int64_t v = in[i]; out[i] = (v < 0 || v > 0x7fffffffLL) ? -1 : (int32_t)v; }
+}
+
+// Bucket-ordered copy of the fp16 query rows (A operand of the rescoring GEMM):
+//   qg[slot, :] = q[slot_pair[slot] / nb, :]      one warp per slot, 16-byte vectors
+__global__ void __launch_bounds__(256)
+gather_queries_kernel(const uint16_t* __restrict__ q, const int32_t* __restrict__ slot_pair,
+                      const PlanScalars* __restrict__ sc, int nb, int d, uint16_t* __restrict__ qg) {
+  const int n_slots = sc->n_slots;
+  const int lane = threadIdx.x & 31;
+  const int vec = d / 8;                           // uint4 per row
+  for (int slot = blockIdx.x * 8 + (threadIdx.x >> 5); slot < n_slots; slot += gridDim.x * 8) {
+    const int qi = slot_pair[slot] / nb;
+    const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)qi * d);
+    uint4* dst = reinterpret_cast<uint4*>(qg + (size_t)slot * d);
+    for (int v = lane; v < vec; v += 32) dst[v] = src[v];
+  }
+}
+
+}  // namespace lmi

@@ -1,0 +1,57 @@
+// rowlist.cuh -- thread-private running top-k' list used by both rescoring kernels.
+//
+// One thread owns one query row (= one TMEM lane in the tcgen05 kernel).  The list lives in
+// shared memory as [k'][128] (entry-major, row-minor) so the 32 lanes of a warp touch 32
+// consecutive banks.  Strategy: keep the list unsorted, remember its minimum; a candidate that
+// beats the minimum overwrites it and the k' entries are rescanned for the new minimum.  After
+// warm-up an insertion happens about k'*ln(n/k') times per row per n objects, i.e. rarely, while
+// the common path is one FMUL + one compare per score.
+//
+// Replaces the per-row ``argsort(kind='quicksort')[:, :k]`` over the full distance matrix
+// (search/li/LearnedIndex.py:170-172) and the running k-th-distance threshold of the shipped
+// search (LearnedIndex.py:71-72, utils.py:22-23): the threshold here is per row and updated
+// after every insertion instead of once per rank.
+#pragma once
+#include "common.cuh"
+
+namespace lmi {
+
+template <int KP>
+struct RowList {
+  float thr;      // current minimum of the list (kNegInf while it still has empty entries)
+  int minpos;     // entry holding that minimum
+
+  __device__ __forceinline__ void reset(float* sc, int32_t* ps, int row, bool live) {
+#pragma unroll 4
+    for (int j = 0; j < KP; ++j) { sc[j * kTileQ + row] = kNegInf; ps[j * kTileQ + row] = -1; }
+    thr = live ? kNegInf : 3.0e38f;    // dead rows never insert
+    minpos = 0;
+  }
+
+  __device__ __forceinline__ void insert(float* sc, int32_t* ps, int row, float s, int32_t pos) {
+    sc[minpos * kTileQ + row] = s;
+    ps[minpos * kTileQ + row] = pos;
+    float m = sc[row];
+    int mp = 0;
+#pragma unroll 4
+    for (int j = 1; j < KP; ++j) {
+      const float v = sc[j * kTileQ + row];
+      if (v < m) { m = v; mp = j; }
+    }
+    thr = m;
+    minpos = mp;
+  }
+
+  // write the row's list (unsorted) to global memory
+  __device__ __forceinline__ void flush(const float* sc, const int32_t* ps, int row, Cand* out) const {
+#pragma unroll 4
+    for (int j = 0; j < KP; ++j) {
+      Cand c;
+      c.score = sc[j * kTileQ + row];
+      c.pos = ps[j * kTileQ + row];
+      out[j] = c;
+    }
+  }
+};
+
+}  // namespace lmi

@@ -1,0 +1,267 @@
+"""Host-side mirror of the reference's index interface for the query-time hot path.
+
+``GpuLearnedIndex`` keeps the names, argument meaning, return types and error behaviour of
+``li.LearnedIndex`` (reference: search/li/LearnedIndex.py:17-195) for ``search`` and
+``search_single``, and ``GpuNavigator`` those of ``li.model.NeuralNetwork.predict_proba`` /
+``predict`` (search/li/model.py:201-229).  All compute happens in liblmi_b200.so (sm_100a CUDA)
+through the C-ABI of include/lmi_b200.h; there is no CPU path.
+
+Semantics implemented: for each query the ``n_buckets`` most probable
+categories of the MLP; candidates = every object whose ``pred_categories`` entry is one of them;
+result = the k smallest ``1 - cos`` (float64 on the float16 inputs) with 1-based ids, ascending,
+ties -> lower bucket rank then lower id; unfilled slots (id 0, dist 10000.0).  That is what the
+reference's ``search(..., use_threshold=False)`` returns, and what ``use_threshold=True`` returns
+on every row its '<k objects' padding defect (LearnedIndex.py:174-190) does not touch;
+``use_threshold`` is accepted and ignored because the threshold is a pruning device, not part of
+the result definition.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import LmiStats, check
+
+RESCORE_SIMT, RESCORE_TC = 0, 1
+SHARD_BUCKETS, SHARD_STRIPES = 0, 1
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def _as_rows(x):
+    """DataFrame / ndarray -> (contiguous ndarray, id_base).  The reference indexes objects by the
+    DataFrame label, which run() makes 1-based (search.py:71-72, :83-84)."""
+    id_base = 1
+    if hasattr(x, "to_numpy") and hasattr(x, "index"):
+        cols = [c for c in x.columns if c != "category"]        # LearnedIndex.py:140-141
+        idx = np.asarray(x.index)
+        if idx.shape[0] and not np.array_equal(idx, np.arange(idx[0], idx[0] + idx.shape[0])):
+            raise ValueError("data_search index must be consecutive integers")
+        id_base = int(idx[0]) if idx.shape[0] else 1
+        x = x[cols].to_numpy() if len(cols) != x.shape[1] else x.to_numpy()
+    return np.ascontiguousarray(x), id_base
+
+
+def extract_mlp(model):
+    """(weights, biases) of the nn.Linear layers of a reference model: accepts li.LearnedIndex,
+    li.model.NeuralNetwork, li.model.Model or a torch Sequential (model.py:15-83)."""
+    import torch
+    m = model
+    for attr in ("model", "model", "layers"):
+        if not isinstance(m, torch.nn.Sequential) and hasattr(m, attr):
+            m = getattr(m, attr)
+    mods = list(m) if isinstance(m, torch.nn.Sequential) else list(m.modules())
+    lin = [x for x in mods if isinstance(x, torch.nn.Linear)]
+    if not lin:
+        raise ValueError("no nn.Linear layers found")
+    for x in mods:
+        if not isinstance(x, (torch.nn.Linear, torch.nn.ReLU, torch.nn.Sequential)):
+            raise ValueError(f"unsupported layer {type(x).__name__}: only Linear/ReLU stacks (model.py:21-78)")
+    w = [x.weight.detach().cpu().numpy().astype(np.float32) for x in lin]
+    b = [x.bias.detach().cpu().numpy().astype(np.float32) for x in lin]
+    return w, b
+
+
+class GpuNavigator:
+    """Stands where ``li.model.NeuralNetwork`` stands at query time (model.py:201-229)."""
+
+    def __init__(self, owner: "GpuLearnedIndex"):
+        self._o = owner
+
+    def predict_proba(self, data_X, n_top=None):
+        """-> (probs f32 [nq,n_top] descending, classes i64 [nq,n_top]); n_top defaults to all C
+        categories like ``prob.topk(prob.shape[1])`` (model.py:226-229)."""
+        o = self._o
+        x = np.ascontiguousarray(np.asarray(data_X, dtype=np.float32))
+        if x.ndim != 2 or x.shape[1] != o.d_nav:
+            raise ValueError(f"expected [n, {o.d_nav}] navigation vectors")
+        n_top = o.n_categories if n_top is None else int(n_top)
+        classes = np.empty((x.shape[0], n_top), dtype=np.int64)
+        probs = np.empty((x.shape[0], n_top), dtype=np.float32)
+        check(o._lib.lmi_navigate(o._h, _ptr(x), x.shape[0], n_top, _ptr(classes), _ptr(probs)))
+        return probs, classes
+
+    def predict(self, data_X):
+        """argmax category per row, int64 (model.py:201-212)."""
+        o = self._o
+        x = np.ascontiguousarray(np.asarray(data_X, dtype=np.float32))
+        out = np.empty(x.shape[0], dtype=np.int64)
+        check(o._lib.lmi_predict(o._h, _ptr(x), x.shape[0], _ptr(out)))
+        return out
+
+
+class GpuLearnedIndex:
+    """Drop-in for ``li.LearnedIndex`` on the query path (LearnedIndex.py:17-195)."""
+
+    def __init__(self, n_categories, d_nav=96, d=768, device=0, rescore=RESCORE_TC,
+                 chunk_objects=None, rank=0, world=1, shard_policy=SHARD_BUCKETS):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        self.n_categories, self.d_nav, self.d, self.device = int(n_categories), int(d_nav), int(d), int(device)
+        check(self._lib.lmi_create(C.byref(self._h), self.device, self.d_nav, self.d, self.n_categories))
+        self.set_option("rescore", rescore)
+        if chunk_objects is not None:
+            self.set_option("chunk_objects", chunk_objects)
+        if world > 1:
+            check(self._lib.lmi_set_shard(self._h, rank, world, shard_policy))
+        self.rank, self.world = rank, world
+        self.model = None                 # like LearnedIndex.model (LearnedIndex.py:19-20)
+        self._store_key = None
+
+    # ---- lifetime ----
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.lmi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, name, value):
+        check(self._lib.lmi_set_option(self._h, name.encode(), int(value)))
+
+    # ---- model ----
+    def set_model(self, weights, biases):
+        """Load the nn.Linear stack (weights[l] = [out,in] fp32).  Sets ``self.model``."""
+        w = [np.ascontiguousarray(np.asarray(x, dtype=np.float32)) for x in weights]
+        b = [np.ascontiguousarray(np.asarray(x, dtype=np.float32)) for x in biases]
+        if w[0].shape[1] != self.d_nav:
+            raise ValueError("first layer input width must equal d_nav")
+        for i in range(1, len(w)):
+            if w[i].shape[1] != w[i - 1].shape[0]:
+                raise ValueError("layer shapes do not chain")
+        n = len(w)
+        dims = (C.c_int32 * n)(*[x.shape[0] for x in w])
+        wp = (C.c_void_p * n)(*[x.ctypes.data for x in w])
+        bp = (C.c_void_p * n)(*[x.ctypes.data for x in b])
+        check(self._lib.lmi_set_mlp(self._h, n, dims, wp, bp))
+        self.model = GpuNavigator(self)
+        return self
+
+    @classmethod
+    def from_reference(cls, li, n_categories=None, d_nav=None, **kw):
+        """Build from an (unmodified) reference ``li.LearnedIndex`` after ``build`` / ``pickle.load``."""
+        w, b = extract_mlp(li)
+        obj = cls(n_categories or w[-1].shape[0], d_nav=d_nav or w[0].shape[1], **kw)
+        return obj.set_model(w, b)
+
+    # ---- store ----
+    def prepare(self, data_search, pred_categories):
+        """Build (or reuse) the device bucket store for (data_search, pred_categories).  The
+        reference regroups and regathers on every rank of every search (LearnedIndex.py:143,152);
+        here it happens once per dataset and is keyed on the inputs' identity."""
+        rows, id_base = _as_rows(data_search)
+        pc = np.ascontiguousarray(np.asarray(pred_categories, dtype=np.int64))
+        key = (id(data_search), rows.shape, int(pc.shape[0]), int(pc[:: max(1, pc.shape[0] // 997)].sum()))
+        if key == self._store_key:
+            return self
+        if rows.dtype != np.float16:
+            rows = rows.astype(np.float16)            # clip768v2 'emb' is float16 (search.py:79-81)
+        if rows.ndim != 2 or rows.shape[1] != self.d:
+            raise ValueError(f"data_search must be [N, {self.d}]")
+        if pc.shape[0] != rows.shape[0]:
+            raise ValueError("pred_categories length != number of objects")
+        check(self._lib.lmi_set_buckets(self._h, _ptr(rows.view(np.uint16)), _ptr(pc), rows.shape[0], id_base))
+        self._store_key = key
+        return self
+
+    def prepare_device(self, data_f16_t, pred_categories_t, id_base=1, chunk_rows=1 << 20):
+        """Same from torch CUDA tensors already in HBM (fp16 [N,d], int64 [N])."""
+        n = int(data_f16_t.shape[0])
+        check(self._lib.lmi_store_begin(self._h, C.c_void_p(pred_categories_t.data_ptr()), n, id_base, 1))
+        import torch
+        torch.cuda.current_stream().synchronize()
+        for lo in range(0, n, chunk_rows):
+            cnt = min(chunk_rows, n - lo)
+            check(self._lib.lmi_store_append(self._h, C.c_void_p(data_f16_t[lo:lo + cnt].data_ptr()), lo, cnt, 1))
+        check(self._lib.lmi_store_end(self._h))
+        self._store_key = ("device", n)
+        return self
+
+    def bucket_ptr(self):
+        out = np.empty(self.n_categories + 1, dtype=np.int64)
+        check(self._lib.lmi_get_bucket_ptr(self._h, _ptr(out)))
+        return out
+
+    # ---- search (reference: LearnedIndex.py:22-101) ----
+    def search(self, data_navigation, queries_navigation, data_search, queries_search, pred_categories,
+               n_buckets=1, k=10, use_threshold=False):
+        assert self.model is not None, 'Model is not trained, call `build` first.'      # LearnedIndex.py:60
+        if data_navigation is not None and hasattr(data_navigation, "columns"):
+            data_navigation['category'] = pred_categories                                # LearnedIndex.py:67
+        self.prepare(data_search, pred_categories)
+        qn = np.ascontiguousarray(np.asarray(queries_navigation, dtype=np.float32))      # model.py:88
+        qs = np.ascontiguousarray(np.asarray(queries_search, dtype=np.float16))
+        nq = qs.shape[0]
+        if qn.shape != (nq, self.d_nav) or qs.shape != (nq, self.d):
+            raise ValueError("query arrays have the wrong shape")
+        dists = np.empty((nq, k), dtype=np.float64)
+        anns = np.empty((nq, k), dtype=np.uint32)
+        check(self._lib.lmi_search(self._h, _ptr(qn), _ptr(qs.view(np.uint16)), nq, int(n_buckets), int(k),
+                                   _ptr(dists), _ptr(anns)))
+        assert anns.shape == dists.shape == (nq, k)                                      # LearnedIndex.py:99
+        return dists, anns
+
+    # ---- search_single (reference: LearnedIndex.py:103-195) ----
+    def search_single(self, data_navigation, data_search, queries_search, pred_categories, k=10,
+                      threshold_dist=None):
+        """``pred_categories`` here is the category of every *query* at one rank (as in the reference).
+        The object->bucket assignment comes from ``data_navigation['category']`` (LearnedIndex.py:143)
+        unless a store was prepared already."""
+        if self._store_key is None:
+            if data_navigation is None or "category" not in getattr(data_navigation, "columns", []):
+                raise AssertionError("no bucket store: call prepare() or pass data_navigation with a 'category' column")
+            self.prepare(data_search, np.asarray(data_navigation["category"]))
+        qs = np.ascontiguousarray(np.asarray(queries_search, dtype=np.float16))
+        nq = qs.shape[0]
+        cat = np.ascontiguousarray(np.asarray(pred_categories, dtype=np.int64))
+        thr = None if threshold_dist is None else np.ascontiguousarray(np.asarray(threshold_dist, dtype=np.float64))
+        dists = np.empty((nq, k), dtype=np.float64)
+        nns = np.empty((nq, k), dtype=np.uint32)
+        check(self._lib.lmi_search_rank(self._h, _ptr(qs.view(np.uint16)), nq, _ptr(cat), int(k), _ptr(thr),
+                                        _ptr(dists), _ptr(nns)))
+        return dists, nns
+
+    # ---- device-resident variants (benchmarks, multi-GPU) ----
+    def search_device(self, q_nav_t, q_f16_t, n_buckets, k, out=None):
+        import torch
+        nq = int(q_f16_t.shape[0])
+        if out is None:
+            out = (torch.empty(nq, k, dtype=torch.float64, device=q_f16_t.device),
+                   torch.empty(nq, k, dtype=torch.int32, device=q_f16_t.device))
+        st = torch.cuda.current_stream(q_f16_t.device).cuda_stream
+        check(self._lib.lmi_search_device(self._h, C.c_void_p(q_nav_t.data_ptr()), C.c_void_p(q_f16_t.data_ptr()), nq,
+                                          int(n_buckets), int(k), C.c_void_p(out[0].data_ptr()),
+                                          C.c_void_p(out[1].data_ptr()), C.c_void_p(st)))
+        return out
+
+    def search_partial_device(self, q_nav_t, q_f16_t, n_buckets, k, partial_t):
+        import torch
+        nq = int(q_f16_t.shape[0])
+        st = torch.cuda.current_stream(q_f16_t.device).cuda_stream
+        check(self._lib.lmi_search_partial_device(self._h, C.c_void_p(q_nav_t.data_ptr()), C.c_void_p(q_f16_t.data_ptr()),
+                                                  nq, int(n_buckets), int(k), C.c_void_p(partial_t.data_ptr()), C.c_void_p(st)))
+
+    def merge_partials_device(self, gathered_t, world, nq, k, out):
+        import torch
+        st = torch.cuda.current_stream(gathered_t.device).cuda_stream
+        check(self._lib.lmi_merge_partials_device(self._h, C.c_void_p(gathered_t.data_ptr()), int(world), int(nq), int(k),
+                                                  C.c_void_p(out[0].data_ptr()), C.c_void_p(out[1].data_ptr()), C.c_void_p(st)))
+        return out
+
+    def partial_bytes(self, nq, k):
+        return int(self._lib.lmi_partial_bytes(int(nq), int(k)))
+
+    def stats(self):
+        s = LmiStats()
+        check(self._lib.lmi_get_stats(self._h, C.byref(s)))
+        d = s.as_dict()
+        d["rescore_kernel"] = self._lib.lmi_rescore_kernel_name(self._h).decode()
+        return d
