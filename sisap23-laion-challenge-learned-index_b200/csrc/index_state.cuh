@@ -75,6 +75,7 @@ struct lmi_index {
   int64_t total_chunks = 0, max_chunks = 0;
   CUtensorMap tmap_x{};                     // store tensor map (TC kernel)
   bool tmap_x_ok = false;
+  bool use_tc_now = false;
 
   // search workspace (grow-only)
   lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;

@@ -16,7 +16,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
   const int d = idx->d;
   bool done = false;
   if constexpr (KP <= 64) {
-   if (idx->rescore == LMI_RESCORE_TC) {
+   if (idx->use_tc_now) {
     done = true;
     constexpr int STAGES = (KP <= 16) ? 4 : 3;
     auto kern = rescore_tc_kernel<KP, STAGES>;
@@ -82,9 +82,10 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
   const int64_t max_plists = std::max<int64_t>(1, nq * idx->h_chunks_sorted_prefix[std::min(nb, C)]);
   LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
-  const bool use_tc = (idx->rescore == LMI_RESCORE_TC && KP <= 64);
+  // an empty shard has no tensor map and no work items: the (idle) CUDA-core kernel is launched instead
+  const bool use_tc = (idx->rescore == LMI_RESCORE_TC && KP <= 64 && idx->tmap_x_ok);
+  idx->use_tc_now = use_tc;
   if (use_tc) {
-    if (!idx->tmap_x_ok) return set_error(LMI_ERR_STATE, "store tensor map missing (empty shard?)");
     // +128 rows of slack: the last tile's TMA box may start up to 127 rows before the end
     LMI_CUDA(idx->qg.reserve((size_t)(n_pairs + kTileQ) * d * 2));
     const size_t rows_cap = idx->qg.cap / ((size_t)d * 2);
