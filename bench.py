@@ -44,7 +44,7 @@ def parse_args():
     p.add_argument("--model-type", default="MLP-5")
     p.add_argument("--blobs", type=int, default=2000)
     p.add_argument("--sigma", type=float, default=0.7)
-    p.add_argument("--rescore", default="tc", choices=["tc", "simt"])
+    p.add_argument("--rescore", default="tc", choices=["tc", "tc_ss", "simt"])
     p.add_argument("--chunk-objects", type=int, default=None)
     p.add_argument("--shard", default="buckets", choices=["buckets", "stripes"])
     p.add_argument("--gt-queries", type=int, default=10_000, help="queries used for recall ground truth")
@@ -260,13 +260,13 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
-    from lmi_b200.index import GpuLearnedIndex, RESCORE_TC, RESCORE_SIMT, SHARD_BUCKETS, SHARD_STRIPES
+    from lmi_b200.index import GpuLearnedIndex, RESCORE_TC, RESCORE_TC_SS, RESCORE_SIMT, SHARD_BUCKETS, SHARD_STRIPES
     peaks = load_peaks()
     inp = build_inputs(args, device, dist)
     nq, k, nb = args.nq, args.k, args.buckets
 
     li = GpuLearnedIndex(args.categories, device=local_rank,
-                         rescore=RESCORE_TC if args.rescore == "tc" else RESCORE_SIMT,
+                         rescore={"tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT}[args.rescore],
                          chunk_objects=args.chunk_objects, rank=rank, world=world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)
     li.set_model(inp["weights"], inp["biases"])

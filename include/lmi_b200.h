@@ -46,7 +46,8 @@ typedef enum {
 
 /* rescoring kernels (option "rescore") */
 #define LMI_RESCORE_SIMT 0    /* CUDA-core reference kernel (cross-check in tests) */
-#define LMI_RESCORE_TC   1    /* tcgen05 / TMEM / TMA kernel (default) */
+#define LMI_RESCORE_TC   1    /* tcgen05 kernel, query tile resident in TMEM, objects streamed by TMA (default) */
+#define LMI_RESCORE_TC_SS 2   /* tcgen05 kernel, both operands streamed through shared memory (d > 768 fallback) */
 
 typedef struct {
   /* shape of the last search */

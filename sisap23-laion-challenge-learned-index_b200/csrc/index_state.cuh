@@ -73,13 +73,14 @@ struct lmi_index {
   std::vector<int64_t> h_bucket_ptr;        // [C+1] local CSR (host copy)
   std::vector<int64_t> h_chunks_sorted_prefix;   // prefix sums of chunks_b sorted descending
   int64_t total_chunks = 0, max_chunks = 0;
-  CUtensorMap tmap_x{};                     // store tensor map (TC kernel)
+  CUtensorMap tmap_x{};                     // store tensor map, box 256 x 64 (SS kernel)
+  CUtensorMap tmap_x64{};                   // store tensor map, box 64 x 64 (TS kernel)
   bool tmap_x_ok = false;
-  bool use_tc_now = false;
+  int kernel_now = LMI_RESCORE_SIMT;         // kernel chosen for the search in flight
 
   // search workspace (grow-only)
   lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;
-  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars;
+  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr;
   lmi::DevBuf nav_cls, nav_probs, nav_x;
   CUtensorMap tmap_q{};
   void* tmap_q_ptr = nullptr; size_t tmap_q_rows = 0;

@@ -5,6 +5,7 @@
 #include "store.cuh"
 #include "rescore_simt.cuh"
 #include "rescore_tc.cuh"
+#include "rescore_ts.cuh"
 #include "finalize.cuh"
 
 namespace lmi {
@@ -34,7 +35,8 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D fp16 row-major [rows, d] tensor, box = [64 halves (128 B), box_rows], 128-byte swizzle
-static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, int box_rows) {
+static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, int box_rows,
+                     CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
@@ -42,7 +44,7 @@ static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, i
   cuuint32_t box[2] = {(cuuint32_t)kTcBlockK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled failed, code " + std::to_string((int)r));
   return LMI_OK;
@@ -92,7 +94,7 @@ void lmi_destroy(lmi_index* idx) {
                     &idx->owner, &idx->bucket_ptr, &idx->stage_rows, &idx->ws_qnav, &idx->ws_q16, &idx->ws_out_d,
                     &idx->ws_out_i, &idx->ws_thr, &idx->ws_cls64, &idx->top_cls, &idx->m_b, &idx->qoff,
                     &idx->chunks_b, &idx->plist_base, &idx->slot_pair, &idx->pair_slot, &idx->items, &idx->plists,
-                    &idx->qg, &idx->scalars, &idx->nav_cls, &idx->nav_probs, &idx->nav_x};
+                    &idx->qg, &idx->scalars, &idx->qthr, &idx->nav_cls, &idx->nav_probs, &idx->nav_x};
   for (DevBuf* b : bufs) b->release();
   if (idx->x) cudaFree(idx->x);
   if (idx->inv_norm) cudaFree(idx->inv_norm);
@@ -107,7 +109,8 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   if (!idx || !name) return set_error(LMI_ERR_ARG, "NULL argument");
   std::string n(name);
   if (n == "rescore") {
-    if (value != LMI_RESCORE_SIMT && value != LMI_RESCORE_TC) return set_error(LMI_ERR_ARG, "rescore: 0 (simt) or 1 (tc)");
+    if (value != LMI_RESCORE_SIMT && value != LMI_RESCORE_TC && value != LMI_RESCORE_TC_SS)
+      return set_error(LMI_ERR_ARG, "rescore: 0 (simt), 1 (tcgen05, queries in TMEM) or 2 (tcgen05, smem operands)");
     idx->rescore = (int)value;
   } else if (n == "chunk_objects") {
     if (value < 256 || value > (1 << 24)) return set_error(LMI_ERR_ARG, "chunk_objects out of range");

@@ -16,20 +16,34 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
   const int d = idx->d;
   bool done = false;
   if constexpr (KP <= 64) {
-   if (idx->use_tc_now) {
-    done = true;
-    constexpr int STAGES = (KP <= 16) ? 4 : 3;
-    auto kern = rescore_tc_kernel<KP, STAGES>;
-    constexpr size_t smem = tc_smem_bytes<KP, STAGES>();
-    static bool attr_done = false;
-    if (!attr_done) {
-      LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_done = true;
+    if (idx->kernel_now == LMI_RESCORE_TC) {
+      done = true;
+      constexpr int STAGES = (KP <= 16) ? 6 : (KP <= 32 ? 5 : 4);
+      auto kern = rescore_ts_kernel<KP, STAGES>;
+      constexpr size_t smem = ts_smem_bytes<KP, STAGES>();
+      static bool attr_done = false;
+      if (!attr_done) {
+        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+      }
+      kern<<<idx->num_sms, kTsThreads, smem, st>>>(idx->tmap_x64, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+                                                   idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
+                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>());
+      idx->rescore_name = "rescore_ts_kernel";
+    } else if (idx->kernel_now == LMI_RESCORE_TC_SS) {
+      done = true;
+      constexpr int STAGES = (KP <= 16) ? 4 : 3;
+      auto kern = rescore_tc_kernel<KP, STAGES>;
+      constexpr size_t smem = tc_smem_bytes<KP, STAGES>();
+      static bool attr_done = false;
+      if (!attr_done) {
+        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+      }
+      kern<<<idx->num_sms, kTcThreads, smem, st>>>(idx->tmap_q, idx->tmap_x, d, idx->inv_norm, idx->items.as<WorkItem>(),
+                                                   idx->scalars.as<PlanScalars>(), idx->plists.as<Cand>());
+      idx->rescore_name = "rescore_tc_kernel";
     }
-    kern<<<idx->num_sms, kTcThreads, smem, st>>>(idx->tmap_q, idx->tmap_x, d, idx->inv_norm, idx->items.as<WorkItem>(),
-                                                 idx->scalars.as<PlanScalars>(), idx->plists.as<Cand>());
-    idx->rescore_name = "rescore_tc_kernel";
-   }
   }
   if (!done) {
     auto kern = rescore_simt_kernel<KP>;
@@ -83,8 +97,15 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   const int64_t max_plists = std::max<int64_t>(1, nq * idx->h_chunks_sorted_prefix[std::min(nb, C)]);
   LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
   // an empty shard has no tensor map and no work items: the (idle) CUDA-core kernel is launched instead
-  const bool use_tc = (idx->rescore == LMI_RESCORE_TC && KP <= 64 && idx->tmap_x_ok);
-  idx->use_tc_now = use_tc;
+  int kernel = LMI_RESCORE_SIMT;
+  if (idx->rescore != LMI_RESCORE_SIMT && KP <= 64 && idx->tmap_x_ok)
+    kernel = (idx->rescore == LMI_RESCORE_TC && d <= 2 * kTsACols) ? LMI_RESCORE_TC : LMI_RESCORE_TC_SS;
+  idx->kernel_now = kernel;
+  const bool use_tc = (kernel == LMI_RESCORE_TC_SS);       // SS kernel: needs the bucket-ordered query copy
+  if (kernel == LMI_RESCORE_TC) {
+    LMI_CUDA(idx->qthr.reserve((size_t)nq * 4));
+    LMI_CUDA(cudaMemsetAsync(idx->qthr.p, 0, (size_t)nq * 4, st));
+  }
   if (use_tc) {
     // +128 rows of slack: the last tile's TMA box may start up to 127 rows before the end
     LMI_CUDA(idx->qg.reserve((size_t)(n_pairs + kTileQ) * d * 2));

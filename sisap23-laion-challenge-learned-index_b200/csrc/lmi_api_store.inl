@@ -132,6 +132,7 @@ int lmi_store_end(lmi_index* idx) {
   idx->cats.release(); idx->pos.release(); idx->block_hist.release(); idx->stage_rows.release();
   if (idx->n_local > 0) {
     int rc = make_tmap(&idx->tmap_x, idx->x, (uint64_t)idx->n_local, idx->d, kTcBlockN);
+    if (rc == LMI_OK) rc = make_tmap(&idx->tmap_x64, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN);
     if (rc != LMI_OK) return rc;
     idx->tmap_x_ok = true;
   }

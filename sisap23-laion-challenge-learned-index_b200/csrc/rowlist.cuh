@@ -18,14 +18,24 @@ namespace lmi {
 
 template <int KP>
 struct RowList {
-  float thr;      // current minimum of the list (kNegInf while it still has empty entries)
-  int minpos;     // entry holding that minimum
+  float thr;      // insertion threshold = max(lmin, seed)
+  float lmin;     // current minimum of the list (kNegInf while it still has empty entries)
+  float seed;     // external lower bound on the row's final k'-th best score (kNegInf = none)
+  int minpos;     // entry holding the list minimum
 
-  __device__ __forceinline__ void reset(float* sc, int32_t* ps, int row, bool live) {
+  __device__ __forceinline__ void reset(float* sc, int32_t* ps, int row, bool live, float seed_ = kNegInf) {
 #pragma unroll 4
     for (int j = 0; j < KP; ++j) { sc[j * kTileQ + row] = kNegInf; ps[j * kTileQ + row] = -1; }
-    thr = live ? kNegInf : 3.0e38f;    // dead rows never insert
+    lmin = kNegInf;
+    seed = live ? seed_ : 3.0e38f;     // dead rows never insert
+    thr = seed;
     minpos = 0;
+  }
+
+  // a better external bound became known
+  __device__ __forceinline__ void raise_seed(float s) {
+    seed = fmaxf(seed, s);
+    thr = fmaxf(thr, seed);
   }
 
   __device__ __forceinline__ void insert(float* sc, int32_t* ps, int row, float s, int32_t pos) {
@@ -38,7 +48,8 @@ struct RowList {
       const float v = sc[j * kTileQ + row];
       if (v < m) { m = v; mp = j; }
     }
-    thr = m;
+    lmin = m;
+    thr = fmaxf(m, seed);
     minpos = mp;
   }
 

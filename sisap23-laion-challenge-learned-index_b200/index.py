@@ -24,7 +24,7 @@ import numpy as np
 from . import _lib
 from ._lib import LmiStats, check
 
-RESCORE_SIMT, RESCORE_TC = 0, 1
+RESCORE_SIMT, RESCORE_TC, RESCORE_TC_SS = 0, 1, 2
 SHARD_BUCKETS, SHARD_STRIPES = 0, 1
 
 

@@ -50,7 +50,7 @@ def test_navigation_matches_reference(tag):
     assert (pc == ref).mean() > 0.995
 
 
-@pytest.mark.parametrize("rescore", [0, 1], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("rescore", [0, 1, 2], ids=["simt", "tcgen05-tmemA", "tcgen05-ss"])
 @pytest.mark.parametrize("tag", GOLDEN_TAGS)
 def test_search_matches_reference_clean(tag, rescore):
     """vs the reference's own search(..., use_threshold=False) on rows where it is defect-free,
@@ -72,7 +72,7 @@ def test_search_matches_reference_clean(tag, rescore):
         st = li.stats()
         assert st["n_uncertified"] == 0, st
         assert st["max_abs_score_err"] < 5e-6, st
-        assert st["rescore_kernel"] == ("rescore_tc_kernel" if rescore else "rescore_simt_kernel")
+        assert st["rescore_kernel"] == ["rescore_simt_kernel", "rescore_ts_kernel", "rescore_tc_kernel"][rescore]
 
 
 @pytest.mark.parametrize("tag", GOLDEN_TAGS)
@@ -92,7 +92,7 @@ def test_search_matches_reference_shipped(tag):
         _check_dists(d[ok], g[f"shipped_dists_nb{nb}"][ok])
 
 
-@pytest.mark.parametrize("rescore", [0, 1], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("rescore", [0, 1, 2], ids=["simt", "tcgen05-tmemA", "tcgen05-ss"])
 @pytest.mark.parametrize("tag", GOLDEN_TAGS)
 def test_search_single_matches_reference(tag, rescore):
     g = load_golden(tag)

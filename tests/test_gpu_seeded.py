@@ -111,7 +111,7 @@ def test_edge_cases():
     pc[pc == 9] = 10
     pc[100] = 9                                                  # category 9 holds exactly one object
     _, classes = O.predict_proba(qn, w, b)
-    for rescore in (0, 1):
+    for rescore in (0, 1, 2):
         li = GpuLearnedIndex(C, rescore=rescore).set_model(w, b)
         for nb in (1, 3, C):
             d_, a_ = li.search(None, qn, data, q, pc, n_buckets=nb, k=10)
@@ -161,7 +161,7 @@ def test_sharded_merge_equals_single(case, world, policy):
     assert (out[0].cpu().numpy() == ref_d).all()
 
 
-@pytest.mark.parametrize("rescore", [0, 1], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("rescore", [0, 1, 2], ids=["simt", "tcgen05-tmemA", "tcgen05-ss"])
 def test_small_chunks_many_work_items(case, rescore):
     """chunk_objects=512 splits every bucket into several work items and partial lists; the result
     must not depend on the chunking."""
