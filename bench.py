@@ -51,6 +51,7 @@ def parse_args():
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--dbg-flags", type=int, default=0, help="kernel experiments only; results are invalid when non-zero")
     return p.parse_args()
 
 
@@ -270,6 +271,8 @@ def run_b200(args):
                          chunk_objects=args.chunk_objects, rank=rank, world=world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)
     li.set_model(inp["weights"], inp["biases"])
+    if args.dbg_flags:
+        li.set_option("dbg_flags", args.dbg_flags)
     t0 = time.time()
     li.prepare_device(inp["data_f16"], inp["pred_categories"], id_base=1)
     torch.cuda.synchronize()

@@ -54,6 +54,7 @@ struct lmi_index {
   int chunk_objects = 8192;
   int kprime_extra = 6;
   int timing = 1;
+  int dbg_flags = 0;                        // experiments only (bit 0: rescoring kernel never inserts)
   int rank = 0, world = 1, policy = LMI_SHARD_BUCKETS;
 
   // model

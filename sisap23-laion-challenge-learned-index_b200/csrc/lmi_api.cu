@@ -119,6 +119,8 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   } else if (n == "kprime_extra") {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
     idx->kprime_extra = (int)value;
+  } else if (n == "dbg_flags") {
+    idx->dbg_flags = (int)value;
   } else if (n == "timing") {
     idx->timing = value ? 1 : 0;
   } else {

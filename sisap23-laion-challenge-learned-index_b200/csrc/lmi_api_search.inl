@@ -18,7 +18,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
   if constexpr (KP <= 64) {
     if (idx->kernel_now == LMI_RESCORE_TC) {
       done = true;
-      constexpr int STAGES = (KP <= 16) ? 6 : (KP <= 32 ? 5 : 4);
+      constexpr int STAGES = (KP <= 16) ? 5 : 4;
       auto kern = rescore_ts_kernel<KP, STAGES>;
       constexpr size_t smem = ts_smem_bytes<KP, STAGES>();
       static bool attr_done = false;
@@ -28,7 +28,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       }
       kern<<<idx->num_sms, kTsThreads, smem, st>>>(idx->tmap_x64, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                    idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>());
+                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
       idx->rescore_name = "rescore_ts_kernel";
     } else if (idx->kernel_now == LMI_RESCORE_TC_SS) {
       done = true;

@@ -50,8 +50,8 @@ constexpr int kTsRefresh = 8;                       // tiles between refreshes o
 
 template <int KP, int STAGES>
 constexpr size_t ts_smem_bytes() {
-  return 1024 /*alignment slack*/ + (size_t)STAGES * kTsStageBytes + (sizeof(float) + sizeof(int32_t)) * KP * kTileQ +
-         2 * kTsBlockN * sizeof(float) + 256 /*barriers + tmem ptr*/;
+  return 1024 /*alignment slack*/ + (size_t)STAGES * kTsStageBytes + (sizeof(float) + sizeof(int32_t)) * (KP + kPend) * kTileQ +
+         4 * 2 * kTsBlockN * sizeof(float) + 256 /*barriers + tmem ptr*/;
 }
 
 // order-preserving float <-> uint32 (0 = "nothing published yet")
@@ -72,16 +72,16 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                   int nb, int d, const float* __restrict__ inv_norm,
                   const WorkItem* __restrict__ items, const PlanScalars* __restrict__ sc,
                   uint32_t* __restrict__ qthr,                     // [nq] shared per-query threshold
-                  Cand* __restrict__ plists) {
+                  Cand* __restrict__ plists, int dbg_flags) {
   extern __shared__ unsigned char ts_smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
   // (offset arithmetic on the shared array keeps the shared address space visible to the compiler)
   unsigned char* smem = ts_smem_raw + ((1024u - (ptx::smem_u32(ts_smem_raw) & 1023u)) & 1023u);
   unsigned char* stage_base = smem;
-  float* l_sc = reinterpret_cast<float*>(smem + (size_t)STAGES * kTsStageBytes);    // [KP][128]
-  int32_t* l_ps = reinterpret_cast<int32_t*>(l_sc + KP * kTileQ);                   // [KP][128]
-  float* s_inv = reinterpret_cast<float*>(l_ps + KP * kTileQ);                      // [2][64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kTsBlockN);
+  float* l_sc = reinterpret_cast<float*>(smem + (size_t)STAGES * kTsStageBytes);    // [KP + kPend][128]
+  int32_t* l_ps = reinterpret_cast<int32_t*>(l_sc + (KP + kPend) * kTileQ);         // [KP + kPend][128]
+  float* s_inv = reinterpret_cast<float*>(l_ps + (KP + kPend) * kTileQ);            // [4 warps][2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 4 * 2 * kTsBlockN);
   uint64_t* full_bar = bars;                       // [STAGES]
   uint64_t* empty_bar = bars + STAGES;             // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;         // [2]
@@ -132,55 +132,64 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_f16(kTileQ, kTsBlockN);
-      int stage = 0; uint32_t phase = 0;
-      int acc = 0; uint32_t acc_phase = 0;
-      uint32_t a_phase = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const WorkItem wi = items[it];
-        const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
-        ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);           // this item's queries are in TMEM
-        a_phase ^= 1;
+    // The whole warp walks the loops (warp-uniform control flow); one elected lane issues.  With
+    // N = 64 a tcgen05.mma is 32 tensor-pipe cycles, so the issue sequence must stay short:
+    // full stages are unrolled with compile-time operand offsets and accumulate flags.
+    constexpr uint32_t idesc = ptx::umma_idesc_f16(kTileQ, kTsBlockN);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    uint32_t a_phase = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const int n_tiles = (items[it].obj_count + kTsBlockN - 1) / kTsBlockN;
+      ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);             // this item's queries are in TMEM
+      a_phase ^= 1;
+      ptx::tc_fence_after();
+      for (int t = 0; t < n_tiles; ++t) {
+        ptx::mbar_wait(ptx::smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
         ptx::tc_fence_after();
-        for (int t = 0; t < n_tiles; ++t) {
-          ptx::mbar_wait(ptx::smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
+        const uint32_t d_tmem = tmem_d + (uint32_t)(acc * kTsBlockN);
+        for (int ks = 0; ks < k_stages; ++ks) {
+          const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
+          ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
           ptx::tc_fence_after();
-          const uint32_t d_tmem = tmem_d + (uint32_t)(acc * kTsBlockN);
-          for (int ks = 0; ks < k_stages; ++ks) {
-            const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
-            ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
-            ptx::tc_fence_after();
-            const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes);
-            for (int a = 0; a < atoms; ++a) {
-              const uint64_t b_desc = ptx::umma_desc_k_sw128(sb + a * kTsAtomBytes);
-              const int k16 = (ks * kTsAtomsPerStage + a) * 4;       // index of the first K=16 slice of this atom
+          if (ptx::elect_one()) {
+            const uint64_t b0 = ptx::umma_desc_k_sw128(ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes));
+            const uint32_t a0 = tmem_base + (uint32_t)(ks * kTsAtomsPerStage * 32);   // 32 columns per atom
+            if (atoms == kTsAtomsPerStage) {
+              // A: 16 halves = 8 TMEM columns per K=16 slice; B: +32 bytes inside the swizzle span
+              // (+2 in the addr>>4 field), next atom +8 KB (+512)
+              if (ks == 0) ptx::umma_f16_ts_c<false>(d_tmem, a0, b0, idesc);
+              else         ptx::umma_f16_ts_c<true>(d_tmem, a0, b0, idesc);
 #pragma unroll
-              for (int k4 = 0; k4 < 4; ++k4) {
-                // A: 16 halves = 8 TMEM columns per slice; B: +32 bytes inside the swizzle span
-                ptx::umma_f16_ts(d_tmem, tmem_base + (uint32_t)((k16 + k4) * 8), b_desc + (uint64_t)(k4 * 2), idesc,
-                                 (k16 + k4) != 0 ? 1u : 0u);
-              }
+              for (int i = 1; i < 4 * kTsAtomsPerStage; ++i)
+                ptx::umma_f16_ts_c<true>(d_tmem, a0 + (uint32_t)(i * 8),
+                                         b0 + (uint64_t)((i >> 2) * (kTsAtomBytes >> 4) + (i & 3) * 2), idesc);
+            } else {
+              for (int i = 0; i < 4 * atoms; ++i)
+                ptx::umma_f16_ts(d_tmem, a0 + (uint32_t)(i * 8),
+                                 b0 + (uint64_t)((i >> 2) * (kTsAtomBytes >> 4) + (i & 3) * 2), idesc,
+                                 (ks | i) != 0 ? 1u : 0u);
             }
             ptx::umma_commit(ptx::smem_u32(&empty_bar[stage]));      // smem stage reusable once MMAs retire
-            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            if (ks == k_stages - 1) ptx::umma_commit(ptx::smem_u32(&tfull_bar[acc]));   // accumulator complete
           }
-          ptx::umma_commit(ptx::smem_u32(&tfull_bar[acc]));          // accumulator complete
-          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
     // ===================== epilogue (4 warps, thread = query row) =====================
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
     const int row = quarter * 32 + lane;
-    const int et = threadIdx.x - 64;              // 0..127 among epilogue threads
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
-    RowList<KP> list;
+    RowBuf<KP> list;
+    float* inv_w = s_inv + quarter * 2 * kTsBlockN;    // this warp's private copy of the tile's inverse norms
     int acc = 0; uint32_t acc_phase = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const WorkItem wi = items[it];
-      const bool live = row < wi.rows;
+      const bool live = row < wi.rows && !(dbg_flags & 1);
       const int qi = live ? slot_pair[wi.slot_base + row] / nb : -1;
       // ---- the item's query rows -> TMEM (all MMAs of the previous item have completed: this
       //      thread has seen the tfull barrier of its last tile) ----
@@ -210,20 +219,23 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       }
       list.reset(l_sc, l_ps, row, live, live ? thr_decode(__ldcg(qthr + qi)) : kNegInf);
       const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
-      // inverse norms are fetched one tile ahead (threads 0..63 of the epilogue own one column each)
-      float inv_next = (et < kTsBlockN && et < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + et) : 0.f;
+      // inverse norms are fetched one tile ahead (each lane owns two columns of its warp's copy)
+      float inv_n0 = (lane < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + lane) : 0.f;
+      float inv_n1 = (lane + 32 < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + lane + 32) : 0.f;
       uint32_t pending = 0u;                       // result of the last threshold exchange, consumed one tile later
       for (int t = 0; t < n_tiles; ++t) {
         const int col0 = t * kTsBlockN;
         const int ncols = min(kTsBlockN, wi.obj_count - col0);
-        float* inv = s_inv + acc * kTsBlockN;
-        if (et < kTsBlockN) {
-          inv[et] = inv_next;
-          const int c_next = col0 + kTsBlockN + et;
-          inv_next = (c_next < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + c_next) : 0.f;
+        float* inv = inv_w + acc * kTsBlockN;
+        inv[lane] = inv_n0;
+        inv[lane + 32] = inv_n1;
+        {
+          const int c_next = col0 + kTsBlockN + lane;
+          inv_n0 = (c_next < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + c_next) : 0.f;
+          inv_n1 = (c_next + 32 < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + c_next + 32) : 0.f;
         }
         list.raise_seed(thr_decode(pending));
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        __syncwarp();
         ptx::mbar_wait(ptx::smem_u32(&tfull_bar[acc]), acc_phase);
         ptx::tc_fence_after();
         const uint32_t taddr = tmem_d + lane_addr + (uint32_t)(acc * kTsBlockN);
@@ -257,16 +269,17 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
           const float m = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), fmaxf(fmaxf(s[4], s[5]), fmaxf(s[6], s[7])));
           if (__any_sync(0xffffffffu, m > list.thr)) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (__any_sync(0xffffffffu, s[j] > list.thr)) {
-                if (s[j] > list.thr) list.insert(l_sc, l_ps, row, s[j], pos0 + g * 8 + j);
-              }
-            }
+            for (int j = 0; j < 8; ++j)
+              if (s[j] > list.thr) list.append(l_sc, l_ps, row, s[j], pos0 + g * 8 + j);
+            // keep room for the next group's (up to 8) appends
+            if (__any_sync(0xffffffffu, list.cnt > kPend - 8)) list.prune(l_sc, l_ps, row);
           }
         }
         // publish this row's bound / pick up the other CTAs' (the atomic's old value is read next tile)
-        if (live && ((t + 1) % kTsRefresh == 0 || t + 1 == n_tiles))
-          pending = atomicMax(qthr + qi, list.lmin > kNegInf ? thr_encode(list.lmin) : 0u);
+        if ((t + 1) % kTsRefresh == 0 || t + 1 == n_tiles) {
+          list.prune(l_sc, l_ps, row);
+          if (live) pending = atomicMax(qthr + qi, list.lmin > kNegInf ? thr_encode(list.lmin) : 0u);
+        }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
       if (live)

@@ -65,4 +65,76 @@ struct RowList {
   }
 };
 
+// RowBuf: the same top-k' list with DEFERRED insertion, used by the TMEM-resident tcgen05 kernel.
+//
+// In a warp of 32 rows a candidate is rare per row but not per warp, and an immediate insertion
+// (write + k' rescan, ~300 cycles of dependent shared-memory latency) stalls all 32 rows each time
+// any one of them has a hit.  Here a hit is only appended to the row's pending area (two stores);
+// the expensive merge ("prune") runs for all 32 rows of the warp at once, when some row's pending
+// area is about to overflow or when the list minimum is needed (threshold exchange, flush).
+// Layout: [k' + kPend][128] entries; pending entries live at k'..k'+cnt-1.  The filter threshold
+// `thr` is the list minimum as of the last prune (stale = lower = conservative).
+constexpr int kPend = 16;
+
+template <int KP>
+struct RowBuf {
+  float thr;      // filter: max(lmin at the last prune, seed)
+  float lmin;     // minimum of the k' list (kNegInf while it has empty entries)
+  float seed;     // external lower bound on the row's final k'-th best score
+  int minpos;     // entry holding lmin
+  int cnt;        // pending entries
+
+  __device__ __forceinline__ void reset(float* sc, int32_t* ps, int row, bool live, float seed_) {
+#pragma unroll 4
+    for (int j = 0; j < KP; ++j) { sc[j * kTileQ + row] = kNegInf; ps[j * kTileQ + row] = -1; }
+    lmin = kNegInf;
+    seed = live ? seed_ : 3.0e38f;     // dead rows never append
+    thr = seed;
+    minpos = 0;
+    cnt = 0;
+  }
+  __device__ __forceinline__ void raise_seed(float s) {
+    seed = fmaxf(seed, s);
+    thr = fmaxf(thr, seed);
+  }
+  __device__ __forceinline__ void append(float* sc, int32_t* ps, int row, float s, int32_t pos) {
+    sc[(KP + cnt) * kTileQ + row] = s;
+    ps[(KP + cnt) * kTileQ + row] = pos;
+    ++cnt;
+  }
+  // warp-collective: merge every row's pending entries into its list
+  __device__ __forceinline__ void prune(float* sc, int32_t* ps, int row) {
+    const int mx = __reduce_max_sync(0xffffffffu, cnt);
+    for (int i = 0; i < mx; ++i) {
+      if (i < cnt) {
+        const float s = sc[(KP + i) * kTileQ + row];
+        if (s > lmin) {
+          sc[minpos * kTileQ + row] = s;
+          ps[minpos * kTileQ + row] = ps[(KP + i) * kTileQ + row];
+          float m = sc[row];
+          int mp = 0;
+#pragma unroll
+          for (int j = 1; j < KP; ++j) {
+            const float v = sc[j * kTileQ + row];
+            if (v < m) { m = v; mp = j; }
+          }
+          lmin = m;
+          minpos = mp;
+        }
+      }
+    }
+    cnt = 0;
+    thr = fmaxf(lmin, seed);
+  }
+  __device__ __forceinline__ void flush(const float* sc, const int32_t* ps, int row, Cand* out) const {
+#pragma unroll 4
+    for (int j = 0; j < KP; ++j) {
+      Cand c;
+      c.score = sc[j * kTileQ + row];
+      c.pos = ps[j * kTileQ + row];
+      out[j] = c;
+    }
+  }
+};
+
 }  // namespace lmi
