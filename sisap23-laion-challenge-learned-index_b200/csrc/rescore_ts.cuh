@@ -46,6 +46,7 @@ constexpr int kTsAtomBytes = kTsBlockN * kTsAtomK * 2;            // 8 KB
 constexpr int kTsStageBytes = kTsAtomsPerStage * kTsAtomBytes;    // 32 KB
 constexpr int kTsThreads = 192;
 constexpr int kTsACols = 384;                       // TMEM columns reserved for the query tile (d <= 768)
+constexpr int kTsItemRing = 2;                      // depth of the producer -> consumers work item ring
 constexpr int kTsRefresh = 8;                       // tiles between refreshes of the shared threshold
 
 template <int KP, int STAGES>
@@ -70,7 +71,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                   const uint16_t* __restrict__ q,                  // [nq, d] fp16 bits (original order)
                   const int32_t* __restrict__ slot_pair,           // slot -> pair index q*nb + r
                   int nb, int d, const float* __restrict__ inv_norm,
-                  const WorkItem* __restrict__ items, const PlanScalars* __restrict__ sc,
+                  const WorkItem* __restrict__ items, PlanScalars* __restrict__ sc,
                   uint32_t* __restrict__ qthr,                     // [nq] shared per-query threshold
                   Cand* __restrict__ plists, int dbg_flags) {
   extern __shared__ unsigned char ts_smem_raw[];
@@ -87,7 +88,10 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
   uint64_t* tfull_bar = bars + 2 * STAGES;         // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;    // [2]
   uint64_t* afull_bar = bars + 2 * STAGES + 4;     // [1]
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 5);
+  uint64_t* ifull_bar = bars + 2 * STAGES + 5;     // [kTsItemRing] work item published by the producer
+  uint64_t* iempty_bar = bars + 2 * STAGES + 5 + kTsItemRing;   // [kTsItemRing] ... read by MMA + 4 epilogue warps
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 5 + 2 * kTsItemRing);
+  int32_t* s_item = reinterpret_cast<int32_t*>(tmem_ptr + 1);   // [kTsItemRing]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_items = sc->n_items;
@@ -99,6 +103,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 1); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(ptx::smem_u32(&tfull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&tempty_bar[s]), 4); }
     ptx::mbar_init(ptx::smem_u32(afull_bar), 4);
+    for (int s = 0; s < kTsItemRing; ++s) { ptx::mbar_init(ptx::smem_u32(&ifull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&iempty_bar[s]), 5); }
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_ptr));
@@ -112,7 +117,17 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      int islot = 0; uint32_t iphase = 0;
+      for (;;) {
+        // dynamic scheduling: CTAs that become free one after the other pick up consecutive items =
+        // the query tiles of one object chunk, so those stream the chunk nearly in lock-step and
+        // all but the first read it from L2
+        ptx::mbar_wait(ptx::smem_u32(&iempty_bar[islot]), iphase ^ 1);
+        const int it = atomicAdd(&sc->work_counter, 1);
+        s_item[islot] = it;
+        ptx::mbar_arrive(ptx::smem_u32(&ifull_bar[islot]));
+        if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+        if (it >= n_items) break;
         const WorkItem wi = items[it];
         const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
         for (int t = 0; t < n_tiles; ++t) {
@@ -139,7 +154,14 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
     uint32_t a_phase = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    int islot = 0; uint32_t iphase = 0;
+    for (;;) {
+      ptx::mbar_wait(ptx::smem_u32(&ifull_bar[islot]), iphase);
+      const int it = s_item[islot];
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&iempty_bar[islot]));
+      if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+      if (it >= n_items) break;
       const int n_tiles = (items[it].obj_count + kTsBlockN - 1) / kTsBlockN;
       ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);             // this item's queries are in TMEM
       a_phase ^= 1;
@@ -187,7 +209,14 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     RowBuf<KP> list;
     float* inv_w = s_inv + quarter * 2 * kTsBlockN;    // this warp's private copy of the tile's inverse norms
     int acc = 0; uint32_t acc_phase = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    int islot = 0; uint32_t iphase = 0;
+    for (;;) {
+      ptx::mbar_wait(ptx::smem_u32(&ifull_bar[islot]), iphase);
+      const int it = s_item[islot];
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&iempty_bar[islot]));
+      if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+      if (it >= n_items) break;
       const WorkItem wi = items[it];
       const bool live = row < wi.rows && !(dbg_flags & 1);
       const int qi = live ? slot_pair[wi.slot_base + row] / nb : -1;
