@@ -22,7 +22,10 @@ struct __align__(16) WorkItem {
   int64_t plist_base;     // partial list id of row 0; row r writes list plist_base + r*plist_stride
   int32_t plist_stride;   // = chunks of this bucket
   int32_t bucket;
+  int32_t flags;          // kItemShared: entries 2i and 2i+1 score the same object chunk
+  int32_t pad;
 };
+constexpr int kItemShared = 1;
 
 struct __align__(8) Cand {  // entry of a partial top-k' list
   float score;              // dot(q, x) * inv_norm(x)  (cosine times |q|)

@@ -76,6 +76,8 @@ struct lmi_index {
   int64_t total_chunks = 0, max_chunks = 0;
   CUtensorMap tmap_x{};                     // store tensor map, box 256 x 64 (SS kernel)
   CUtensorMap tmap_x64{};                   // store tensor map, box 64 x 64 (TS kernel)
+  CUtensorMap tmap_xpf{};                   // store tensor map, box 64 x 256 unswizzled (TS kernel, L2 prefetch)
+  CUtensorMap tmap_x32{};                   // store tensor map, box 32 x 64 (TS kernel, shared pairs)
   bool tmap_x_ok = false;
   int kernel_now = LMI_RESCORE_SIMT;         // kernel chosen for the search in flight
 

@@ -36,15 +36,16 @@ static EncodeTiledFn get_encode_fn() {
 
 // 2-D fp16 row-major [rows, d] tensor, box = [64 halves (128 B), box_rows], 128-byte swizzle
 static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, int box_rows,
-                     CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B) {
+                     int box_cols = kTcBlockK, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+  const CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)d * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kTcBlockK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, promo,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled failed, code " + std::to_string((int)r));
   return LMI_OK;

@@ -26,7 +26,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
         LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done = true;
       }
-      kern<<<idx->num_sms, kTsThreads, smem, st>>>(idx->tmap_x64, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+      kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x64, idx->tmap_x32, idx->tmap_xpf, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                    idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
                                                    idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
       idx->rescore_name = "rescore_ts_kernel";
@@ -89,8 +89,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(idx->pair_slot.reserve((size_t)n_pairs * 4));
   LMI_CUDA(idx->scalars.reserve(sizeof(PlanScalars)));
   const int64_t qtiles_max = (nq + kTileQ - 1) / kTileQ;
-  const int64_t items_a = qtiles_max * idx->total_chunks;
-  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(idx->max_chunks, 1);
+  // entries: at most qtiles_b * chunks_b + 1 (dummy) per bucket
+  const int64_t items_a = qtiles_max * idx->total_chunks + C;
+  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(idx->max_chunks, 1) + C;
   const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
   if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));

@@ -133,6 +133,10 @@ int lmi_store_end(lmi_index* idx) {
   if (idx->n_local > 0) {
     int rc = make_tmap(&idx->tmap_x, idx->x, (uint64_t)idx->n_local, idx->d, kTcBlockN);
     if (rc == LMI_OK) rc = make_tmap(&idx->tmap_x64, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN);
+    if (rc == LMI_OK) rc = make_tmap(&idx->tmap_x32, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN / 2);
+    // L2 prefetch boxes: 64 rows x up to 256 halves, no swizzle (nothing lands in shared memory)
+    if (rc == LMI_OK) rc = make_tmap(&idx->tmap_xpf, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN,
+                                     std::min(idx->d, kTsAtomsPerStage * kTsAtomK), CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc != LMI_OK) return rc;
     idx->tmap_x_ok = true;
   }

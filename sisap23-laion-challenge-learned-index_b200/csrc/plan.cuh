@@ -60,7 +60,14 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       tot_pairs += m * nobj;
       if (m > 0) tot_objs += nobj;
     }
-    long long vals[3] = {m, qt * ch, m * ch};
+    // work list entries come in PAIRS (entries 2i, 2i+1 = one item of a 2-CTA cluster of the
+    // TMEM-resident rescoring kernel; the other kernels treat every entry as an independent item):
+    //   shared pair : query tiles 2p and 2p+1 of the same object chunk  (flag kItemShared: the
+    //                 cluster loads the chunk once and multicasts it to both CTAs)
+    //   plain pair  : the odd last query tile of chunks c and c+1 (or a dummy entry)
+    const long long pairs_per_chunk = qt / 2;
+    const long long n_pair = ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
+    long long vals[3] = {m, 2 * n_pair, m * ch};
     long long excl[3];
     for (int w = 0; w < 3; ++w) {
       s_scan[tid] = vals[w];
@@ -81,21 +88,34 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       plist_base[b] = excl[2];
       const long long obj0 = bucket_ptr[b];
       long long it = excl[1];
-      // query tile innermost: consecutive items (-> CTAs running at the same time) share an
-      // object chunk, so it is fetched from HBM once and re-read from L2 by the other tiles.
-      for (int c = 0; c < ch; ++c) {
-        for (int t = 0; t < qt; ++t, ++it) {
-          if (it >= max_items) continue;
+      // order: for every two chunks, their shared pairs first, then the plain pair of their odd
+      // tiles -- consecutive items are picked up by clusters that become free one after the other,
+      // so everything that streams one chunk runs at about the same time and all but the first
+      // reader find it in L2.
+      auto emit = [&](long long c, long long t, int flags) {
+        if (it < max_items) {
           WorkItem wi;
-          wi.slot_base = (int)excl[0] + t * kTileQ;
-          wi.rows = (int)min((long long)kTileQ, m - (long long)t * kTileQ);
-          wi.obj_begin = (int)(obj0 + (long long)c * chunk);
-          wi.obj_count = (int)min((long long)chunk, nobj - (long long)c * chunk);
-          wi.plist_base = excl[2] + (long long)t * kTileQ * ch + c;
-          wi.plist_stride = (int)ch;
-          wi.bucket = b;
+          if (c < 0) {                                     // dummy
+            wi.slot_base = 0; wi.rows = 0; wi.obj_begin = (int)obj0; wi.obj_count = 0;
+            wi.plist_base = 0; wi.plist_stride = 0; wi.bucket = b; wi.flags = 0;
+          } else {
+            wi.slot_base = (int)excl[0] + (int)t * kTileQ;
+            wi.rows = (int)min((long long)kTileQ, m - t * kTileQ);
+            wi.obj_begin = (int)(obj0 + c * chunk);
+            wi.obj_count = (int)min((long long)chunk, nobj - c * chunk);
+            wi.plist_base = excl[2] + t * kTileQ * ch + c;
+            wi.plist_stride = (int)ch;
+            wi.bucket = b;
+            wi.flags = flags;
+          }
           items[it] = wi;
         }
+        ++it;
+      };
+      for (long long c0 = 0; c0 < ch; c0 += 2) {
+        for (long long c = c0; c < min(ch, c0 + 2); ++c)
+          for (long long p = 0; p < pairs_per_chunk; ++p) { emit(c, 2 * p, kItemShared); emit(c, 2 * p + 1, kItemShared); }
+        if (qt & 1) { emit(c0, qt - 1, 0); emit(c0 + 1 < ch ? c0 + 1 : -1, qt - 1, 0); }
       }
     }
     __syncthreads();

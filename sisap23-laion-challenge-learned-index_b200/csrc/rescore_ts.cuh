@@ -18,14 +18,22 @@
 // Structure (persistent, one CTA per SM, warp-specialised):
 //   warp 0   : TMA producer   -- 128B-swizzled K-major boxes of 64 objects x 64 halves; one
 //                                stage = 64 objects x 256 halves (4 boxes, 32 KB)
-//   warp 1   : MMA issuer     -- one elected thread issues tcgen05.mma (M=128, N=64, K=16),
-//                                A from TMEM, B from shared memory, D double-buffered in TMEM
+//   warps 1,6: MMA issuers    -- an elected thread issues tcgen05.mma (M=128, N=64, K=16), A from
+//                                TMEM, B from shared memory; D double-buffered in TMEM, warp 1
+//                                owns the even tiles / accumulator 0, warp 6 the odd ones
 //   warps 2-5: epilogue       -- per item: write the item's 128 query rows into TMEM
 //                                (tcgen05.st); per tile: tcgen05.ld of the finished accumulator
 //                                (thread = TMEM lane = query row), scale by inv_norm, compare
 //                                against the row's running threshold, rare insertion
 // Pipelines: smem full/empty mbarriers (TMA <-> MMA), TMEM full/empty mbarriers (MMA <->
 // epilogue), a_full (epilogue -> MMA: the item's queries are in TMEM).
+//
+// 2-CTA clusters: the grid is launched as clusters of two CTAs; a cluster takes one PAIR of work
+// list entries (plan.cuh).  For a shared pair (two query tiles of the same object chunk) each
+// CTA loads half of every object box and TMA-multicasts it into both CTAs' shared memory, which
+// halves the L2->SM traffic (the bound of the single-CTA version: 128 FLOP/B against ~12 TB/s).
+// Plain pairs load unicast.  Either way the two CTAs consume the stages in lock-step: a stage is
+// refilled only when both MMA warps have retired it (tcgen05.commit multicast on the empty barrier).
 //
 // Running threshold: besides its own list minimum a row uses a per-QUERY lower bound shared by
 // all CTAs (qthr, order-preserving uint32 image of an fp32 score, atomicMax): once any list of
@@ -44,9 +52,10 @@ constexpr int kTsAtomK = 64;                        // halves per swizzle atom r
 constexpr int kTsAtomsPerStage = 4;                 // 256 halves of K per stage
 constexpr int kTsAtomBytes = kTsBlockN * kTsAtomK * 2;            // 8 KB
 constexpr int kTsStageBytes = kTsAtomsPerStage * kTsAtomBytes;    // 32 KB
-constexpr int kTsThreads = 192;
+constexpr int kTsThreads = 224;                     // producer, MMA issuer 0, 4 epilogue warps, MMA issuer 1
 constexpr int kTsACols = 384;                       // TMEM columns reserved for the query tile (d <= 768)
 constexpr int kTsItemRing = 2;                      // depth of the producer -> consumers work item ring
+constexpr int kTsPrefetch = 8;                      // tiles the L2 prefetch runs ahead of the loads
 constexpr int kTsRefresh = 8;                       // tiles between refreshes of the shared threshold
 
 template <int KP, int STAGES>
@@ -66,8 +75,10 @@ __device__ __forceinline__ float thr_decode(uint32_t u) {
 }
 
 template <int KP, int STAGES>
-__global__ void __launch_bounds__(kTsThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTsThreads, 1)
 rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket store [n_local, d], box 64 x 64
+                  const __grid_constant__ CUtensorMap tmap_xh,     // same, box 32 x 64 (half of a shared tile)
+                  const __grid_constant__ CUtensorMap tmap_pf,     // same, box 64 x 256 unswizzled (L2 prefetch)
                   const uint16_t* __restrict__ q,                  // [nq, d] fp16 bits (original order)
                   const int32_t* __restrict__ slot_pair,           // slot -> pair index q*nb + r
                   int nb, int d, const float* __restrict__ inv_norm,
@@ -94,24 +105,40 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
   int32_t* s_item = reinterpret_cast<int32_t*>(tmem_ptr + 1);   // [kTsItemRing]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_items = sc->n_items;
+  const uint32_t crank = ptx::cluster_ctarank();                     // 0 = leader (fetches the work items)
+  const int n_pairs = sc->n_items >> 1;
   const int k_atoms = d / kTsAtomK;                                  // 12 for clip768
   const int k_stages = (k_atoms + kTsAtomsPerStage - 1) / kTsAtomsPerStage;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_x);
-    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 1); }
+    ptx::prefetch_tensormap(&tmap_xh);
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 2); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(ptx::smem_u32(&tfull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&tempty_bar[s]), 4); }
     ptx::mbar_init(ptx::smem_u32(afull_bar), 4);
-    for (int s = 0; s < kTsItemRing; ++s) { ptx::mbar_init(ptx::smem_u32(&ifull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&iempty_bar[s]), 5); }
+    // item ring: the leader's producer publishes into both CTAs; its iempty collects the 6 local
+    // consumer warps + the peer's 7 (the peer's producer is a consumer of the ring too)
+    for (int s = 0; s < kTsItemRing; ++s) { ptx::mbar_init(ptx::smem_u32(&ifull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&iempty_bar[s]), 13); }
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_ptr));
   ptx::tc_fence_before();
   __syncthreads();
+  ptx::cluster_sync();                               // the peer's barriers are initialised too
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const uint32_t tmem_d = tmem_base + kTsACols;
+
+  // every consumer warp: next pair index from the ring, then release the slot to the leader
+  const uint32_t iempty_leader = ptx::mapa(ptx::smem_u32(iempty_bar), 0);
+  auto next_pair = [&](int& islot, uint32_t& iphase) -> int {
+    ptx::mbar_wait_cluster(ptx::smem_u32(&ifull_bar[islot]), iphase);
+    const int pr = s_item[islot];
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive_cluster(iempty_leader + (uint32_t)islot * 8u);
+    if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+    return pr;
+  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -119,57 +146,95 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       int stage = 0; uint32_t phase = 0;
       int islot = 0; uint32_t iphase = 0;
       for (;;) {
-        // dynamic scheduling: CTAs that become free one after the other pick up consecutive items =
-        // the query tiles of one object chunk, so those stream the chunk nearly in lock-step and
-        // all but the first read it from L2
-        ptx::mbar_wait(ptx::smem_u32(&iempty_bar[islot]), iphase ^ 1);
-        const int it = atomicAdd(&sc->work_counter, 1);
-        s_item[islot] = it;
-        ptx::mbar_arrive(ptx::smem_u32(&ifull_bar[islot]));
-        if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
-        if (it >= n_items) break;
-        const WorkItem wi = items[it];
-        const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
+        // dynamic scheduling: clusters that become free one after the other pick up consecutive
+        // pairs = everything that scores one object chunk, so those stream the chunk nearly in
+        // lock-step and all but the first read it from L2
+        int pr;
+        if (crank == 0) {
+          ptx::mbar_wait_cluster(ptx::smem_u32(&iempty_bar[islot]), iphase ^ 1);
+          pr = atomicAdd(&sc->work_counter, 1);
+          s_item[islot] = pr;
+          ptx::st_cluster_u32(ptx::mapa(ptx::smem_u32(&s_item[islot]), 1), (uint32_t)pr);
+          ptx::mbar_arrive(ptx::smem_u32(&ifull_bar[islot]));
+          ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ifull_bar[islot]), 1));
+          if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+        } else {
+          ptx::mbar_wait_cluster(ptx::smem_u32(&ifull_bar[islot]), iphase);
+          pr = s_item[islot];
+          ptx::mbar_arrive_cluster(iempty_leader + (uint32_t)islot * 8u);
+          if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
+        }
+        if (pr >= n_pairs) break;
+        const WorkItem wi = items[2 * pr + crank];
+        const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
+        const int n_tiles = (max(wi.obj_count, peer_count) + kTsBlockN - 1) / kTsBlockN;
+        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & 16);
+        // L2 prefetch kTsPrefetch tiles ahead: the loads that fill the smem ring then see L2 latency,
+        // not HBM latency (the ring holds ~1.6 tiles: 160 KB / 1.8 us of loaded HBM latency is only
+        // 45 B/clk per SM, the MMA consumes 64 B/clk).  One CTA of a shared pair prefetches for both.
+        const bool do_pf = (dbg_flags & 32) && (!shared || crank == 0);   // measured: no gain on B200 (kept as an experiment)
+        auto prefetch_tile = [&](int t) {
+          for (int ks = 0; ks < k_stages; ++ks)
+            ptx::tma_prefetch_2d(&tmap_pf, ks * kTsAtomsPerStage * kTsAtomK, wi.obj_begin + t * kTsBlockN);
+        };
+        if (do_pf) for (int t = 0; t < min(kTsPrefetch, n_tiles); ++t) prefetch_tile(t);
         for (int t = 0; t < n_tiles; ++t) {
           const int obj0 = wi.obj_begin + t * kTsBlockN;
+          if (do_pf && t + kTsPrefetch < n_tiles) prefetch_tile(t + kTsPrefetch);
           for (int ks = 0; ks < k_stages; ++ks) {
             const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
-            ptx::mbar_wait(ptx::smem_u32(&empty_bar[stage]), phase ^ 1);
+            ptx::mbar_wait(ptx::smem_u32(&empty_bar[stage]), phase ^ 1);    // retired by BOTH CTAs
             const uint32_t fb = ptx::smem_u32(&full_bar[stage]);
+            if (dbg_flags & 4) {                                     // experiment: no loads at all
+              ptx::mbar_arrive(fb);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+              continue;
+            }
             ptx::mbar_arrive_expect_tx(fb, (uint32_t)(atoms * kTsAtomBytes));
             const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes);
-            for (int a = 0; a < atoms; ++a)
-              ptx::tma_load_2d(sb + a * kTsAtomBytes, &tmap_x, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+            if (shared) {
+              // this CTA fetches rows [32*crank, 32*crank+32) of the tile for both CTAs
+              for (int a = 0; a < atoms; ++a)
+                ptx::tma_load_2d_mc(sb + a * kTsAtomBytes + crank * (kTsAtomBytes / 2), &tmap_xh, fb,
+                                    (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0 + (int)crank * (kTsBlockN / 2), (uint16_t)3);
+            } else {
+              for (int a = 0; a < atoms; ++a)
+                ptx::tma_load_2d(sb + a * kTsAtomBytes, &tmap_x, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    // The whole warp walks the loops (warp-uniform control flow); one elected lane issues.  With
-    // N = 64 a tcgen05.mma is 32 tensor-pipe cycles, so the issue sequence must stay short:
-    // full stages are unrolled with compile-time operand offsets and accumulate flags.
+  } else if (warp == 1 || warp == 6) {
+    // ===================== MMA issuers (two warps) =====================
+    // With N = 64 a tcgen05.mma is only 32 tensor-pipe cycles, and one thread cannot wait, compute
+    // operands, issue 48 of them and commit inside the 1536 cycles of a tile (measured: ~2200).
+    // So tiles alternate between two issuing warps: warp 1 takes the even tiles (accumulator 0),
+    // warp 6 the odd ones (accumulator 1).  Their instruction streams are independent -- different
+    // accumulators, disjoint smem stages, own barriers -- and the tensor pipe interleaves them.
+    // Within a warp the control flow is warp-uniform and one elected lane issues.
     constexpr uint32_t idesc = ptx::umma_idesc_f16(kTileQ, kTsBlockN);
-    int stage = 0; uint32_t phase = 0;
-    int acc = 0; uint32_t acc_phase = 0;
+    const int parity = (warp == 6) ? 1 : 0;
+    const uint32_t d_tmem = tmem_d + (uint32_t)(parity * kTsBlockN);
+    uint32_t g = 0;                                // running tile number (all items); g & 1 = accumulator
+    int stage = 0; uint32_t phase = 0;             // smem stage / phase of tile g's first K stage
     uint32_t a_phase = 0;
     int islot = 0; uint32_t iphase = 0;
     for (;;) {
-      ptx::mbar_wait(ptx::smem_u32(&ifull_bar[islot]), iphase);
-      const int it = s_item[islot];
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&iempty_bar[islot]));
-      if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
-      if (it >= n_items) break;
-      const int n_tiles = (items[it].obj_count + kTsBlockN - 1) / kTsBlockN;
+      const int pr = next_pair(islot, iphase);
+      if (pr >= n_pairs) break;
+      const int n_tiles = (max(items[2 * pr].obj_count, items[2 * pr + 1].obj_count) + kTsBlockN - 1) / kTsBlockN;
       ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);             // this item's queries are in TMEM
       a_phase ^= 1;
-      ptx::tc_fence_after();
-      for (int t = 0; t < n_tiles; ++t) {
-        ptx::mbar_wait(ptx::smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
+      for (int t = 0; t < n_tiles; ++t, ++g) {
+        if ((int)(g & 1u) != parity) {             // the other warp's tile: just step over its stages
+          stage += k_stages;
+          if (stage >= STAGES) { stage -= STAGES; phase ^= 1; }
+          continue;
+        }
+        ptx::mbar_wait(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_d + (uint32_t)(acc * kTsBlockN);
         for (int ks = 0; ks < k_stages; ++ks) {
           const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
           ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
@@ -177,9 +242,10 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
           if (ptx::elect_one()) {
             const uint64_t b0 = ptx::umma_desc_k_sw128(ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes));
             const uint32_t a0 = tmem_base + (uint32_t)(ks * kTsAtomsPerStage * 32);   // 32 columns per atom
-            if (atoms == kTsAtomsPerStage) {
-              // A: 16 halves = 8 TMEM columns per K=16 slice; B: +32 bytes inside the swizzle span
-              // (+2 in the addr>>4 field), next atom +8 KB (+512)
+            // A: 16 halves = 8 TMEM columns per K=16 slice; B: +32 bytes inside the swizzle span
+            // (+2 in the addr>>4 field), next atom +8 KB (+512)
+            if (dbg_flags & 8) {
+            } else if (atoms == kTsAtomsPerStage) {
               if (ks == 0) ptx::umma_f16_ts_c<false>(d_tmem, a0, b0, idesc);
               else         ptx::umma_f16_ts_c<true>(d_tmem, a0, b0, idesc);
 #pragma unroll
@@ -192,13 +258,12 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                                  b0 + (uint64_t)((i >> 2) * (kTsAtomBytes >> 4) + (i & 3) * 2), idesc,
                                  (ks | i) != 0 ? 1u : 0u);
             }
-            ptx::umma_commit(ptx::smem_u32(&empty_bar[stage]));      // smem stage reusable once MMAs retire
-            if (ks == k_stages - 1) ptx::umma_commit(ptx::smem_u32(&tfull_bar[acc]));   // accumulator complete
+            ptx::umma_commit_mc(ptx::smem_u32(&empty_bar[stage]), (uint16_t)3);   // stage retired here -> both CTAs' producers
+            if (ks == k_stages - 1) ptx::umma_commit(ptx::smem_u32(&tfull_bar[parity]));   // accumulator complete
           }
           __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
@@ -211,13 +276,10 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     int acc = 0; uint32_t acc_phase = 0;
     int islot = 0; uint32_t iphase = 0;
     for (;;) {
-      ptx::mbar_wait(ptx::smem_u32(&ifull_bar[islot]), iphase);
-      const int it = s_item[islot];
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&iempty_bar[islot]));
-      if (++islot == kTsItemRing) { islot = 0; iphase ^= 1; }
-      if (it >= n_items) break;
-      const WorkItem wi = items[it];
+      const int pr = next_pair(islot, iphase);
+      if (pr >= n_pairs) break;
+      const WorkItem wi = items[2 * pr + crank];
+      const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
       const bool live = row < wi.rows && !(dbg_flags & 1);
       const int qi = live ? slot_pair[wi.slot_base + row] / nb : -1;
       // ---- the item's query rows -> TMEM (all MMAs of the previous item have completed: this
@@ -247,14 +309,14 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(afull_bar));
       }
       list.reset(l_sc, l_ps, row, live, live ? thr_decode(__ldcg(qthr + qi)) : kNegInf);
-      const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
+      const int n_tiles = (max(wi.obj_count, peer_count) + kTsBlockN - 1) / kTsBlockN;   // the pair runs in lock-step
       // inverse norms are fetched one tile ahead (each lane owns two columns of its warp's copy)
       float inv_n0 = (lane < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + lane) : 0.f;
       float inv_n1 = (lane + 32 < wi.obj_count) ? __ldg(inv_norm + wi.obj_begin + lane + 32) : 0.f;
       uint32_t pending = 0u;                       // result of the last threshold exchange, consumed one tile later
       for (int t = 0; t < n_tiles; ++t) {
         const int col0 = t * kTsBlockN;
-        const int ncols = min(kTsBlockN, wi.obj_count - col0);
+        const int ncols = max(0, min(kTsBlockN, wi.obj_count - col0));     // 0: padding tile of the shorter entry
         float* inv = inv_w + acc * kTsBlockN;
         inv[lane] = inv_n0;
         inv[lane + 32] = inv_n1;
@@ -277,34 +339,46 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tempty_bar[acc]));
-        // groups of 8 columns: one max + one warp vote decide whether anybody has a candidate at all
-        // (a real, warp-uniform branch: the insertion path must not be if-converted into the hot loop)
-        const bool full_tile = (ncols == kTsBlockN);
+        // Straight-line part first (64 products, 8 group maxima, 8 votes: no branch, so the loads and
+        // multiplies of all groups overlap), then the rare paths.  A group of 8 columns is entered only
+        // if some row of the warp has a candidate in it (warp-uniform branch; the append path must
+        // not be if-converted into the hot loop).
+        if (dbg_flags & 2) { if (++acc == 2) { acc = 0; acc_phase ^= 1; } continue; }   // experiment: accumulator drained, nothing scored
+        float s[kTsBlockN];
+#pragma unroll
+        for (int c4 = 0; c4 < kTsBlockN / 4; ++c4) {
+          const float4 iv = *reinterpret_cast<const float4*>(inv + c4 * 4);
+          const uint32_t* v = (c4 < 8) ? (v0 + c4 * 4) : (v1 + (c4 - 8) * 4);
+          s[c4 * 4 + 0] = __uint_as_float(v[0]) * iv.x;
+          s[c4 * 4 + 1] = __uint_as_float(v[1]) * iv.y;
+          s[c4 * 4 + 2] = __uint_as_float(v[2]) * iv.z;
+          s[c4 * 4 + 3] = __uint_as_float(v[3]) * iv.w;
+        }
+        if (ncols != kTsBlockN) {
+#pragma unroll
+          for (int c = 0; c < kTsBlockN; ++c) if (c >= ncols) s[c] = kNegInf;
+        }
+        uint32_t gmask = 0u;
 #pragma unroll
         for (int g = 0; g < kTsBlockN / 8; ++g) {
-          float s[8];
-          const float4 i0 = *reinterpret_cast<const float4*>(inv + g * 8);
-          const float4 i1 = *reinterpret_cast<const float4*>(inv + g * 8 + 4);
-          const float iv[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+          const float* p = s + g * 8;
+          const float m = fmaxf(fmaxf(fmaxf(p[0], p[1]), fmaxf(p[2], p[3])), fmaxf(fmaxf(p[4], p[5]), fmaxf(p[6], p[7])));
+          gmask |= __any_sync(0xffffffffu, m > list.thr) ? (1u << g) : 0u;
+        }
+        if (gmask != 0u) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int c = g * 8 + j;
-            s[j] = __uint_as_float(c < 32 ? v0[c & 31] : v1[c & 31]) * iv[j];
-          }
-          if (!full_tile) {
+          for (int g = 0; g < kTsBlockN / 8; ++g) {
+            if (gmask & (1u << g)) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) if (g * 8 + j >= ncols) s[j] = kNegInf;
-          }
-          const float m = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), fmaxf(fmaxf(s[4], s[5]), fmaxf(s[6], s[7])));
-          if (__any_sync(0xffffffffu, m > list.thr)) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (s[j] > list.thr) list.append(l_sc, l_ps, row, s[j], pos0 + g * 8 + j);
-            // keep room for the next group's (up to 8) appends
-            if (__any_sync(0xffffffffu, list.cnt > kPend - 8)) list.prune(l_sc, l_ps, row);
+              for (int j = 0; j < 8; ++j)
+                if (s[g * 8 + j] > list.thr) list.append(l_sc, l_ps, row, s[g * 8 + j], pos0 + g * 8 + j);
+              // keep room for the next group's (up to 8) appends
+              if (__any_sync(0xffffffffu, list.cnt > kPend - 8)) list.prune(l_sc, l_ps, row);
+            }
           }
         }
         // publish this row's bound / pick up the other CTAs' (the atomic's old value is read next tile)
+        if (dbg_flags & 64) { if (__any_sync(0xffffffffu, list.cnt >= 3)) list.prune(l_sc, l_ps, row); }
         if ((t + 1) % kTsRefresh == 0 || t + 1 == n_tiles) {
           list.prune(l_sc, l_ps, row);
           if (live) pending = atomicMax(qthr + qi, list.lmin > kNegInf ? thr_encode(list.lmin) : 0u);
@@ -318,6 +392,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
 
   ptx::tc_fence_before();
   __syncthreads();
+  ptx::cluster_sync();                               // no CTA exits while the peer may still signal it
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc<512>(tmem_base); }
 }
 
