@@ -43,7 +43,7 @@ def parse_args():
     p.add_argument("--k", type=int, default=10)
     p.add_argument("--model-type", default="MLP-5")
     p.add_argument("--blobs", type=int, default=2000)
-    p.add_argument("--sigma", type=float, default=0.7)
+    p.add_argument("--sigma", type=float, default=0.55)
     p.add_argument("--rescore", default="tc", choices=["tc", "tc_ss", "simt"])
     p.add_argument("--chunk-objects", type=int, default=None)
     p.add_argument("--shard", default="buckets", choices=["buckets", "stripes"])
@@ -280,17 +280,11 @@ def run_b200(args):
 
     qn, qs = inp["queries_nav"].contiguous(), inp["queries_f16"].contiguous()
     out = (torch.empty(nq, k, dtype=torch.float64, device=device), torch.empty(nq, k, dtype=torch.int32, device=device))
-    if world > 1:
-        part = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device=device)
-        gathered = torch.empty(world * part.numel(), dtype=torch.uint8, device=device)
+    from lmi_b200.shard import DistributedSearch
+    ds = DistributedSearch(li)       # world > 1: partial search -> ONE all-gather (NCCL) -> merge kernel
 
     def step():
-        if world == 1:
-            li.search_device(qn, qs, nb, k, out)
-        else:   # one exchange step: all-gather of the per-rank top-k, then the merge kernel
-            li.search_partial_device(qn, qs, nb, k, part)
-            dist.all_gather_into_tensor(gathered, part)
-            li.merge_partials_device(gathered, world, nq, k, out)
+        ds.search_device(qn, qs, nb, k, out)
 
     def barrier():
         if world > 1:

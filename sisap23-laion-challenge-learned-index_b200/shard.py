@@ -1,0 +1,108 @@
+"""Multi-GPU layer of the query path: one process per GPU, buckets (or bucket stripes) sharded
+across ranks, ONE exchange step per search (an all-gather of every rank's top-k), then a merge.
+
+The reference has nothing distributed; this is new.  It is exact because
+buckets are disjoint object sets (``pred_categories`` assigns one category per object,
+search/li/LearnedIndex.py:240) and the answer is a top-k over their union, so the top-k of the
+per-rank top-k lists is the global top-k.  The merge key (float64 distance, bucket rank, id) makes
+the result independent of the number of ranks.
+
+Host-side pieces (numpy, no GPU needed -- these are what the world_size-2 ``gloo`` tests run):
+  * ``lpt_owners``      -- the bucket -> rank map, identical to the one liblmi_b200.so computes in
+                           ``lmi_store_begin`` (csrc/lmi_api_store.inl: longest-processing-time on n_b^2)
+  * ``shard_keep_mask`` -- which objects a rank holds under either policy
+  * ``merge_partials``  -- numpy mirror of ``merge_partials_kernel`` (csrc/finalize.cuh)
+Device piece:
+  * ``DistributedSearch`` -- search_partial -> ``dist.all_gather_into_tensor`` (NCCL) -> merge kernel
+"""
+from __future__ import annotations
+
+import numpy as np
+
+SHARD_BUCKETS, SHARD_STRIPES = 0, 1
+
+# layout of one exchanged entry (csrc/common.cuh: struct Partial, 16 bytes)
+PARTIAL_DTYPE = np.dtype([("dist", "<f8"), ("id", "<u4"), ("rank", "<u4")])
+EMPTY_DIST = 10_000.0            # LearnedIndex.py:138
+EMPTY_RANK = 0xFFFFFFFF
+
+
+def lpt_owners(sizes, world):
+    """Bucket -> rank, longest-processing-time first on weight n_b^2 (expected work of a bucket
+    ~ n_b * m_b and queries follow the data distribution).  Stable for equal sizes."""
+    sizes = np.asarray(sizes, dtype=np.int64)
+    order = np.argsort(-sizes, kind="stable")
+    load = np.zeros(world, dtype=np.float64)
+    owner = np.zeros(sizes.shape[0], dtype=np.int32)
+    for c in order:
+        best = int(np.argmin(load))          # first minimum, like the C++ loop
+        owner[c] = best
+        load[best] += float(sizes[c]) * float(sizes[c])
+    return owner
+
+
+def shard_keep_mask(pred_categories, n_categories, rank, world, policy=SHARD_BUCKETS):
+    """Boolean mask over objects: True where this rank holds the object.
+    buckets: whole buckets by ``lpt_owners``; stripes: rows [n*rank/world, n*(rank+1)/world) of
+    every bucket, in ascending object order (csrc/store.cuh: store_layout_kernel)."""
+    pc = np.asarray(pred_categories, dtype=np.int64)
+    if world <= 1:
+        return np.ones(pc.shape[0], dtype=bool)
+    sizes = np.bincount(pc, minlength=n_categories).astype(np.int64)
+    if policy == SHARD_BUCKETS:
+        return lpt_owners(sizes, world)[pc] == rank
+    # rank of every object inside its bucket (stable order = ascending object id)
+    order = np.argsort(pc, kind="stable")
+    start = np.concatenate([[0], np.cumsum(sizes)[:-1]])
+    in_bucket = np.empty(pc.shape[0], dtype=np.int64)
+    in_bucket[order] = np.arange(pc.shape[0]) - start[pc[order]]
+    n = sizes[pc]
+    lo, hi = n * rank // world, n * (rank + 1) // world
+    return (in_bucket >= lo) & (in_bucket < hi)
+
+
+def pack_partials(dists, ids, ranks):
+    """(f64 [nq,k], u32 [nq,k], u32 [nq,k]) -> structured array [nq,k] in the exchange layout."""
+    out = np.empty(dists.shape, dtype=PARTIAL_DTYPE)
+    out["dist"], out["id"], out["rank"] = dists, ids, ranks
+    return out
+
+
+def merge_partials(gathered, k):
+    """gathered: structured [world, nq, k] (rank-major, as the all-gather delivers it).
+    Returns (dists f64 [nq,k], ids u32 [nq,k]): the k smallest by (dist, bucket rank, id, source
+    position) -- the total order ``key_less`` of csrc/finalize.cuh."""
+    world, nq, kk = gathered.shape
+    flat = np.transpose(gathered, (1, 0, 2)).reshape(nq, world * kk)
+    src = np.broadcast_to(np.arange(world * kk), flat.shape)
+    order = np.lexsort((src, flat["id"], flat["rank"], flat["dist"]), axis=1)[:, :k]
+    sel = np.take_along_axis(flat, order, axis=1)
+    return sel["dist"].astype(np.float64), sel["id"].astype(np.uint32)
+
+
+class DistributedSearch:
+    """One search step on ``world`` GPUs: every rank navigates all queries, rescoring covers the
+    rank's own buckets, one ``all_gather_into_tensor`` of [nq, k] x 16 B, merge on every rank."""
+
+    def __init__(self, index, group=None):
+        import torch.distributed as dist
+        self.li, self.dist, self.group = index, dist, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self._bufs = None
+
+    def search_device(self, q_nav_t, q_f16_t, n_buckets, k, out=None):
+        import torch
+        nq = int(q_f16_t.shape[0])
+        dev = q_f16_t.device
+        if out is None:
+            out = (torch.empty(nq, k, dtype=torch.float64, device=dev), torch.empty(nq, k, dtype=torch.int32, device=dev))
+        if self.world == 1:
+            return self.li.search_device(q_nav_t, q_f16_t, n_buckets, k, out)
+        nbytes = self.li.partial_bytes(nq, k)
+        if self._bufs is None or self._bufs[0].numel() != nbytes:
+            self._bufs = (torch.empty(nbytes, dtype=torch.uint8, device=dev),
+                          torch.empty(self.world * nbytes, dtype=torch.uint8, device=dev))
+        part, gathered = self._bufs
+        self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
+        self.dist.all_gather_into_tensor(gathered, part, group=self.group)      # the one exchange step
+        return self.li.merge_partials_device(gathered, self.world, nq, k, out)
