@@ -358,7 +358,11 @@ def run_b200(args):
         roof = dict(bound="tensor", achieved=flops / t_k / 1e12, peak=peaks["tflops"], unit="TFLOP/s")
     else:
         roof = dict(bound="hbm", achieved=bytes_algo / t_k / 1e9, peak=peaks["hbm_gbs"], unit="GB/s")
-    roof.update(frac=roof["achieved"] / roof["peak"], traffic=None, kernel=st["rescore_kernel"],
+    traffic = None            # DRAM bytes per launch of the dominant kernel, from the committed ncu capture
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath) and world == 1 and args.n == 10_000_000 and nb == 4 and nq == 10_000:
+        traffic = json.load(open(tpath)).get(st["rescore_kernel"])
+    roof.update(frac=roof["achieved"] / roof["peak"], traffic=traffic, kernel=st["rescore_kernel"],
                 kernel_ms=t_k * 1e3, peak_source=peaks["source"], algorithmic_flops=flops,
                 algorithmic_bytes=bytes_algo, hbm_gbs_achieved=bytes_algo / t_k / 1e9,
                 t_roof_ms=max(t_gemm, t_hbm) * 1e3)
@@ -378,7 +382,7 @@ def run_b200(args):
                        "l2": "inputs larger than L2 (15.4 GB bucket store streamed every step)",
                        "shard": args.shard if world > 1 else "none", "rescore": args.rescore,
                        "synthetic": {"blobs": args.blobs, "sigma": args.sigma}},
-            "e2e": e2e, "gpu_launches": args.steps * (8 + (1 if world > 1 else 0)),
+            "e2e": e2e, "gpu_launches": args.steps * (7 + (1 if world > 1 else 0)),   # nav, 4 plan kernels, rescoring, finalize (+ merge)
             "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "stages_ms": {k_: st[k_] for k_ in ("ms_navigate", "ms_plan", "ms_rescore", "ms_finalize", "ms_total")},
             "exactness": {"n_uncertified": st["n_uncertified"], "max_abs_score_err": st["max_abs_score_err"]},
