@@ -9,7 +9,10 @@
 #include "../../sisap23-laion-challenge-learned-index_b200/csrc/ptx_sm100.cuh"
 using namespace lmi;
 
-constexpr int STAGES = 6, STAGE_BYTES = 32768, ATOM = 8192;
+constexpr int STAGE_BYTES = 32768, ATOM = 8192;
+#ifndef STAGES
+#define STAGES 6
+#endif
 
 template <int MC>   // 0 unicast, 1 multicast half-boxes (32 rows), 2 multicast alternating whole atoms (64 rows)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1)
@@ -28,7 +31,8 @@ tma_kernel(const __grid_constant__ CUtensorMap t64, const __grid_constant__ CUte
   ptx::cluster_sync();
   const int pair = blockIdx.x >> 1;
   // MC: both CTAs of a pair stream the same rows; unicast: every CTA its own rows (or the pair's, same_chunk)
-  const long long row_base = (long long)((MC || same_chunk) ? pair : blockIdx.x) * tiles_per_cta * 64;
+  // same_chunk = g >= 1: groups of g consecutive CTAs stream the same rows (g = 0: private rows)
+  const long long row_base = (long long)(MC ? pair : (same_chunk ? (int)(blockIdx.x / same_chunk) : (int)blockIdx.x)) * tiles_per_cta * 64;
   long long t0 = clock64();
   if (threadIdx.x == 0) {
     int stage = 0; uint32_t phase = 0;
@@ -99,9 +103,10 @@ int main() {
   const int tiles = 2048;
   for (int rows : {32768, 6000000}) {   // 50 MB (L2-resident) / 9.2 GB (HBM)
     run<0>("unicast 64-row boxes, private rows", buf, rows, tiles, 0);
-    run<0>("unicast 64-row boxes, pair reads same rows", buf, rows, tiles, 1);
+    run<0>("unicast 64-row boxes, 2 CTAs share rows", buf, rows, tiles, 2);
+    run<0>("unicast 64-row boxes, 3 CTAs share rows", buf, rows, tiles, 3);
+    run<0>("unicast 64-row boxes, 4 CTAs share rows", buf, rows, tiles, 4);
     run<1>("multicast 2 x 32-row boxes (pair shares)", buf, rows, tiles, 1);
-    run<2>("multicast alternating 64-row atoms (pair shares)", buf, rows, tiles, 1);
   }
   return 0;
 }
