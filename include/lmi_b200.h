@@ -61,6 +61,10 @@ typedef struct {
   double  max_abs_score_err;     /* max |fp32 cosine - fp64 cosine| over refined candidates */
   /* device time of the last search, milliseconds (CUDA events on the search stream) */
   float ms_navigate, ms_plan, ms_rescore, ms_finalize, ms_total;
+  /* mean rescoring-kernel duration over the searches issued since the previous lmi_get_stats call
+   * (at most the last 256), and how many went into it; option "timing" = 1 */
+  float ms_rescore_avg;
+  int32_t n_rescore_timed;
 } lmi_stats;
 
 const char* lmi_last_error(void);

@@ -29,6 +29,7 @@ class LmiStats(C.Structure):
         ("max_abs_score_err", C.c_double),
         ("ms_navigate", C.c_float), ("ms_plan", C.c_float), ("ms_rescore", C.c_float),
         ("ms_finalize", C.c_float), ("ms_total", C.c_float),
+        ("ms_rescore_avg", C.c_float), ("n_rescore_timed", C.c_int32),
     ]
 
     def as_dict(self):

@@ -92,6 +92,10 @@ struct lmi_index {
   // stats
   lmi::PlanScalars* h_scalars = nullptr;    // pinned
   cudaEvent_t ev[5]{};
+  // ring of (start, stop) pairs around the rescoring kernel of the searches since the last lmi_get_stats
+  static constexpr int kEvRing = 256;
+  cudaEvent_t ev_k3[kEvRing][2]{};
+  int64_t n_since_stats = 0;
   cudaStream_t last_stream = nullptr;
   lmi_stats stats{};
   bool stats_pending = false;

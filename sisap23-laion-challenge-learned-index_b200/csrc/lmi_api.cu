@@ -80,6 +80,7 @@ int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories) 
   idx->d_nav = d_nav; idx->d = d; idx->C = n_categories;
   LMI_CUDA(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
   for (auto& e : idx->ev) LMI_CUDA(cudaEventCreate(&e));
+  for (auto& pr : idx->ev_k3) for (auto& e : pr) LMI_CUDA(cudaEventCreate(&e));
   LMI_CUDA(cudaMallocHost(&idx->h_scalars, sizeof(PlanScalars)));
   memset(idx->h_scalars, 0, sizeof(PlanScalars));
   *out = idx;
@@ -102,6 +103,7 @@ void lmi_destroy(lmi_index* idx) {
   if (idx->ids) cudaFree(idx->ids);
   if (idx->h_scalars) cudaFreeHost(idx->h_scalars);
   for (auto& e : idx->ev) if (e) cudaEventDestroy(e);
+  for (auto& pr : idx->ev_k3) for (auto& e : pr) if (e) cudaEventDestroy(e);
   if (idx->stream) cudaStreamDestroy(idx->stream);
   delete idx;
 }

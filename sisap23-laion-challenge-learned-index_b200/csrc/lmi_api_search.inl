@@ -142,7 +142,8 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
     gather_queries_kernel<<<idx->num_sms * 4, 256, 0, st>>>(q16_dev, idx->slot_pair.as<int32_t>(),
                                                             idx->scalars.as<PlanScalars>(), nb, d, idx->qg.as<uint16_t>());
   LMI_CUDA(cudaGetLastError());
-  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[2], st));
+  cudaEvent_t* ring = idx->ev_k3[idx->n_since_stats % lmi_index::kEvRing];
+  if (timing) { LMI_CUDA(cudaEventRecord(idx->ev[2], st)); LMI_CUDA(cudaEventRecord(ring[0], st)); }
   // ---- K3 rescoring ----
   int rc = LMI_OK;
   switch (KP) {
@@ -152,7 +153,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
     default: rc = launch_rescore<128>(idx, q16_dev, nb, st); break;
   }
   if (rc != LMI_OK) return rc;
-  if (timing) LMI_CUDA(cudaEventRecord(idx->ev[3], st));
+  if (timing) { LMI_CUDA(cudaEventRecord(ring[1], st)); LMI_CUDA(cudaEventRecord(idx->ev[3], st)); ++idx->n_since_stats; }
   // ---- K4 + K5 finalize ----
   finalize_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, st>>>(
       nq, nb, k, KP, d, top, idx->pair_slot.as<int32_t>(), idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(),
@@ -299,7 +300,19 @@ int lmi_get_stats(lmi_index* idx, lmi_stats* out) {
       for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&ms[i], idx->ev[i], idx->ev[i + 1]);
       idx->stats.ms_navigate = ms[0]; idx->stats.ms_plan = ms[1]; idx->stats.ms_rescore = ms[2]; idx->stats.ms_finalize = ms[3];
       cudaEventElapsedTime(&idx->stats.ms_total, idx->ev[0], idx->ev[4]);
+      // average rescoring-kernel duration over every search since the previous lmi_get_stats (ring-limited)
+      const int64_t n = std::min<int64_t>(idx->n_since_stats, lmi_index::kEvRing);
+      double sum = 0;
+      for (int64_t i = 0; i < n; ++i) {
+        float t = 0;
+        cudaEventElapsedTime(&t, idx->ev_k3[(idx->n_since_stats - 1 - i) % lmi_index::kEvRing][0],
+                             idx->ev_k3[(idx->n_since_stats - 1 - i) % lmi_index::kEvRing][1]);
+        sum += t;
+      }
+      idx->stats.ms_rescore_avg = n ? (float)(sum / n) : 0.f;
+      idx->stats.n_rescore_timed = (int32_t)n;
     }
+    idx->n_since_stats = 0;
     idx->stats_pending = false;
   }
   *out = idx->stats;

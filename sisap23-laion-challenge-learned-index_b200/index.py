@@ -265,3 +265,39 @@ class GpuLearnedIndex:
         d = s.as_dict()
         d["rescore_kernel"] = self._lib.lmi_rescore_kernel_name(self._h).decode()
         return d
+
+
+class GpuBaseline:
+    """Exhaustive search with the rescoring kernels: mirror of ``li.Baseline`` (search/li/Baseline.py:7-25;
+    SURVEY.md 8(f) row N4).  ``search(queries, data, k)`` -> ``(dists f64 [nq,k], nns [nq,k] 1-based, seconds)``
+    = the k smallest ``1 - cos`` over ALL objects.  Internally a one-bucket index (every object in category
+    0, every query routed to it), so the same tcgen05 kernel, float64 refine and certificate apply; equal
+    distances resolve to the lower id (the reference's ``argsort`` order among exact ties is unspecified).
+    ``bench.py``'s ground truth deliberately does NOT use this class (it must stay independent of K3)."""
+
+    def __init__(self, device=0, rescore=RESCORE_TC):
+        self.device, self.rescore = device, rescore
+        self._li, self._key = None, None
+
+    def build(self, data):
+        """Baseline.build is a no-op that returns its duration (Baseline.py:22-25); here it uploads."""
+        import time
+        s = time.time()
+        rows, _ = _as_rows(data)
+        key = (id(data), rows.shape)
+        if key != self._key:
+            if self._li is not None:
+                self._li.close()
+            self._li = GpuLearnedIndex(1, d=rows.shape[1], device=self.device, rescore=self.rescore)
+            # Baseline.search numbers the rows 1..N regardless of the DataFrame's labels (Baseline.py:18)
+            self._li.prepare(np.asarray(rows), np.zeros(rows.shape[0], dtype=np.int64))
+            self._key = key
+        return time.time() - s
+
+    def search(self, queries, data, k=10):
+        import time
+        s = time.time()
+        self.build(data)
+        qs = np.asarray(queries)
+        dists, nns = self._li.search_single(None, None, qs, np.zeros(qs.shape[0], dtype=np.int64), k=k)
+        return dists, nns, time.time() - s

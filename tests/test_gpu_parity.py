@@ -121,6 +121,21 @@ def test_exhaustive_equals_reference_baseline():
     _check_dists(d, g["baseline_dists"])
 
 
+def test_gpu_baseline_equals_reference_baseline():
+    """N4: GpuBaseline.search mirrors li.Baseline.search (Baseline.py:14-20) -- same ids (1-based row
+    numbers), float64 distances, and a duration as third return value."""
+    from lmi_b200.index import GpuBaseline
+    g = load_golden("ref_mlp5_n1600_c16")
+    sub = g["baseline_ids"].shape[0]
+    bl = GpuBaseline(device=0)
+    d, a, secs = bl.search(g["queries_f16"][:sub], g["data_f16"], k=g["k"])
+    assert secs > 0 and a.dtype == np.uint32 and d.dtype == np.float64
+    assert_ids_equal_up_to_ties(a, d, g["baseline_ids"], g["baseline_dists"], what="GpuBaseline")
+    _check_dists(d, g["baseline_dists"])
+    d2, a2, _ = bl.search(g["queries_f16"][:sub], g["data_f16"], k=g["k"])        # store reused
+    assert np.array_equal(a, a2) and np.array_equal(d, d2)
+
+
 def test_errors_mirror_reference():
     g = load_golden("ref_mlp5_n1600_c16")
     from lmi_b200.index import GpuLearnedIndex
