@@ -47,6 +47,11 @@ def parse_args():
     p.add_argument("--rescore", default="tc", choices=["tc", "tc_ss", "simt"])
     p.add_argument("--chunk-objects", type=int, default=None)
     p.add_argument("--shard", default="buckets", choices=["buckets", "stripes"])
+    p.add_argument("--presharded", action="store_true",
+                   help="every rank generates and loads only its own row range (automatic above 30M rows: "
+                        "BASELINE.json configs[3], 100M on 8 GPUs = 19.2 GB per GPU)")
+    p.add_argument("--parity-queries", type=int, default=16,
+                   help="queries re-derived by an independent float64 bucket-restricted brute force inside the run")
     p.add_argument("--gt-queries", type=int, default=10_000, help="queries used for recall ground truth")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
@@ -144,7 +149,89 @@ def build_inputs(args, device, dist=None):
     return t
 
 
-def ground_truth(data_f16, queries_f16, k, chunk=500_000, extra=6):
+def build_inputs_presharded(args, device, dist, rank, world):
+    """Rows [n*rank/world, n*(rank+1)/world) only (chunk-seeded generator: the rows do not depend on who
+    draws them).  PCA and MLP weights come from rank 0 and are broadcast; pred_categories is local."""
+    import torch
+    from lmi_b200.synth import SynthSpec, SynthWorld
+    from lmi_b200.trainer import train_index, make_mlp, mlp_params
+    from lmi_b200.shard import range_of_rank
+    spec = SynthSpec(n=args.n, nq=args.nq, n_blobs=args.blobs, sigma=args.sigma)
+    w_ = SynthWorld(spec, device)
+    w_.fit_pca(w_.draw_range(0, min(spec.n, spec.pca_rows)))
+    if dist:
+        dist.broadcast(w_.mean, src=0); dist.broadcast(w_.proj, src=0)
+    lo, hi = range_of_rank(args.n, rank, world)
+    data = w_.draw_range(lo, hi)
+    nav = torch.empty(hi - lo, spec.d_nav, dtype=torch.float32, device=device)
+    for a in range(0, hi - lo, 1 << 18):
+        nav[a:a + (1 << 18)] = w_.project(data[a:a + (1 << 18)])
+    genq = torch.Generator(device=device).manual_seed(spec.seed_queries)
+    queries = w_._draw(spec.nq, genq)
+    q_nav = w_.project(queries)
+    if dist:                                     # identical query bits everywhere
+        dist.broadcast(queries, src=0); dist.broadcast(q_nav, src=0)
+    if rank == 0:                                # rank 0's rows are an i.i.d. sample of the dataset
+        model, w, b = train_index(nav, args.categories, args.model_type)
+    else:
+        model = make_mlp(nav.shape[1], args.categories, args.model_type).to(device)
+    if dist:
+        for prm in model.parameters():
+            dist.broadcast(prm.data, src=0)
+        w, b = mlp_params(model)
+    model.eval()
+    pc = torch.empty(hi - lo, dtype=torch.int64, device=device)
+    with torch.no_grad():
+        for a in range(0, hi - lo, 1 << 20):
+            pc[a:a + (1 << 20)] = model(nav[a:a + (1 << 20)]).argmax(1)
+    del nav
+    return dict(data_f16=data, queries_f16=queries, queries_nav=q_nav, weights=w, biases=b, pred_categories=pc,
+                spec=spec, row_lo=lo, row_hi=hi)
+
+
+def merge_topk_across_ranks(dist_, d_loc, i_loc, k, world, tiebreak=None):
+    """All ranks hold (dist f64 [q,k], id i64 [q,k]) over their own rows -> global k smallest by (dist, id)."""
+    import torch
+    gd = torch.empty(world, *d_loc.shape, dtype=d_loc.dtype, device=d_loc.device)
+    gi = torch.empty(world, *i_loc.shape, dtype=i_loc.dtype, device=i_loc.device)
+    dist_.all_gather_into_tensor(gd, d_loc.contiguous()); dist_.all_gather_into_tensor(gi, i_loc.contiguous())
+    gd = gd.permute(1, 0, 2).reshape(d_loc.shape[0], -1); gi = gi.permute(1, 0, 2).reshape(d_loc.shape[0], -1)
+    order = torch.argsort(gi, dim=1, stable=True)                     # (dist, id): sort by id, then stably by dist
+    gd, gi = gd.gather(1, order), gi.gather(1, order)
+    order = torch.argsort(gd, dim=1, stable=True)[:, :k]
+    return gd.gather(1, order), gi.gather(1, order)
+
+
+def bucket_restricted_truth(data_f16, pc, id_base, queries_f16, classes, k):
+    """Independent float64 restatement of the result definition over the rows this process
+    holds: for query q the k smallest 1 - cos64 among {x : pc[x] in classes[q]}.  Plain torch, no lmi kernel.
+    -> (dist f64 [g,k], ids i64 [g,k]; unfilled = (10000.0, 0))."""
+    import torch
+    g = queries_f16.shape[0]
+    out_d = torch.full((g, k), 10000.0, dtype=torch.float64, device=data_f16.device)
+    out_i = torch.zeros((g, k), dtype=torch.int64, device=data_f16.device)
+    for r in range(g):
+        rows = torch.nonzero(torch.isin(pc, classes[r])).squeeze(1)
+        if rows.numel() == 0:
+            continue
+        q = queries_f16[r].double(); q = q / q.norm().clamp_min(1e-300)
+        best_d, best_i = [], []
+        for a in range(0, rows.numel(), 200_000):
+            rr = rows[a:a + 200_000]
+            x = data_f16[rr].double()
+            x = x / x.norm(dim=1, keepdim=True).clamp_min(1e-300)
+            dd = 1.0 - x @ q
+            kk = min(k, dd.numel())
+            v, j = torch.topk(dd, kk, largest=False)
+            best_d.append(v); best_i.append(rr[j] + id_base)
+        dd, ii = torch.cat(best_d), torch.cat(best_i)
+        o = torch.argsort(ii, stable=True); dd, ii = dd[o], ii[o]
+        o = torch.argsort(dd, stable=True)[:k]
+        out_d[r, :o.numel()] = dd[o]; out_i[r, :o.numel()] = ii[o]
+    return out_d, out_i
+
+
+def ground_truth(data_f16, queries_f16, k, chunk=500_000, extra=6, id_base=1, return_dists=False):
     """Exhaustive cosine k-NN, independent of the rescoring kernels: fp32 matmul (TF32 off) per
     object chunk keeping k+extra candidates, then a float64 re-score of the survivors.
     Stands in for Baseline.search (Baseline.py:14-20), which needs O(N*nq) float64 memory."""
@@ -165,6 +252,7 @@ def ground_truth(data_f16, queries_f16, k, chunk=500_000, extra=6):
     # float64 refine
     qd = queries_f16.double(); qd = qd / qd.norm(dim=1, keepdim=True).clamp_min(1e-300)
     out = torch.empty(q.shape[0], k, dtype=torch.int64, device=q.device)
+    out_d = torch.empty(q.shape[0], k, dtype=torch.float64, device=q.device) if return_dists else None
     for lo in range(0, q.shape[0], 1000):
         xi = best_i[lo:lo + 1000]
         xd = data_f16[xi.reshape(-1)].double().reshape(xi.shape[0], kk, -1)
@@ -173,7 +261,11 @@ def ground_truth(data_f16, queries_f16, k, chunk=500_000, extra=6):
         # ties: lower id first (deterministic)
         order = torch.argsort(dist + xi.double() * 1e-18, dim=1)[:, :k]
         out[lo:lo + 1000] = xi.gather(1, order)
-    return out + 1                                # 1-based ids like the reference (search.py:71-72)
+        if return_dists:
+            out_d[lo:lo + 1000] = dist.gather(1, order)
+    if return_dists:
+        return out_d, out + id_base
+    return out + id_base                          # 1-based ids like the reference (search.py:71-72)
 
 
 def recall_at_k(found_ids, truth_ids, k):
@@ -263,18 +355,23 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=device)
     from lmi_b200.index import GpuLearnedIndex, RESCORE_TC, RESCORE_TC_SS, RESCORE_SIMT, SHARD_BUCKETS, SHARD_STRIPES
     peaks = load_peaks()
-    inp = build_inputs(args, device, dist)
+    presharded = args.presharded or args.n > 30_000_000
+    if presharded and args.n * 768 * 2 * 2.1 / world > 170e9:
+        raise SystemExit(f"bench.py: {args.n} rows need more than {world} GPU(s) (2 x 1536 B per row per GPU)")
+    inp = build_inputs_presharded(args, device, dist, rank, world) if presharded else build_inputs(args, device, dist)
     nq, k, nb = args.nq, args.k, args.buckets
+    id_base = inp.get("row_lo", 0) + 1
 
+    # presharded: an ordinary (unsharded) index over this rank's rows; the exchange + merge are the same
     li = GpuLearnedIndex(args.categories, device=local_rank,
                          rescore={"tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT}[args.rescore],
-                         chunk_objects=args.chunk_objects, rank=rank, world=world,
+                         chunk_objects=args.chunk_objects, rank=0 if presharded else rank, world=1 if presharded else world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)
     li.set_model(inp["weights"], inp["biases"])
     if args.dbg_flags:
         li.set_option("dbg_flags", args.dbg_flags)
     t0 = time.time()
-    li.prepare_device(inp["data_f16"], inp["pred_categories"], id_base=1)
+    li.prepare_device(inp["data_f16"], inp["pred_categories"], id_base=id_base)
     torch.cuda.synchronize()
     store_seconds = time.time() - t0
 
@@ -370,10 +467,35 @@ def run_b200(args):
 
     # ---- quality: recall@10 against an independent brute force; certificate ----
     recall = None
-    if rank == 0:
-        g = min(args.gt_queries, nq)
+    g = min(args.gt_queries, nq)
+    if presharded:
+        t_d, t_i = ground_truth(inp["data_f16"], qs[:g], k, id_base=id_base, return_dists=True)
+        if world > 1:
+            t_d, t_i = merge_topk_across_ranks(dist, t_d, t_i, k, world)
+        recall = recall_at_k(out[1][:g], t_i, k)
+    elif rank == 0:
         truth = ground_truth(inp["data_f16"], qs[:g], k)
         recall = recall_at_k(out[1][:g], truth, k)
+
+    # ---- parity inside the run, at full size: a sample of queries re-derived by an independent float64
+    #      brute force restricted to the buckets the navigation chose (the result definition) ----
+    parity = None
+    gp = min(args.parity_queries, nq)
+    if gp > 0 and (presharded or rank == 0):
+        sel = torch.linspace(0, nq - 1, gp, device=device).long()
+        _, cls = li.model.predict_proba(qn[sel].cpu().numpy(), n_top=nb)
+        cls = torch.from_numpy(cls.astype(np.int64)).to(device)
+        p_d, p_i = bucket_restricted_truth(inp["data_f16"], inp["pred_categories"], id_base, qs[sel], cls, k)
+        if presharded and world > 1:
+            p_d, p_i = merge_topk_across_ranks(dist, p_d, p_i, k, world)
+        got_i, got_d = out[1][sel].to(torch.int64), out[0][sel]
+        diff = got_i != p_i
+        # a differing id is a documented tie only if both distances agree to 1e-12 (SURVEY 8(c) exception (i))
+        bad = diff & ((got_d - p_d).abs() > 1e-12)
+        parity = dict(queries=gp, ids_compared=int(diff.numel()), ids_equal=int((~diff).sum().item()),
+                      tie_swaps=int((diff & ~bad).sum().item()), mismatches=int(bad.sum().item()),
+                      max_abs_dist_diff=float((got_d - p_d).abs().max().item()),
+                      checker="torch float64 brute force over the probed buckets (bench.bucket_restricted_truth)")
 
     # ---- roofline of the dominant kernel (tensor bound) ----
     t_k = float(np.mean(rescore_ms)) * 1e-3
@@ -415,6 +537,7 @@ def run_b200(args):
             "e2e": e2e, "gpu_launches": args.steps * (7 + (1 if world > 1 else 0)),   # nav, 4 plan kernels, rescoring, finalize (+ merge)
             "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "stages_ms": {k_: st[k_] for k_ in ("ms_navigate", "ms_plan", "ms_rescore", "ms_finalize", "ms_total")},
+            "parity_sample": parity, "presharded": presharded,
             "exactness": {"n_uncertified": st["n_uncertified"], "max_abs_score_err": st["max_abs_score_err"]},
             "store_build_seconds": store_seconds, "work_items": st["n_work_items"],
         }

@@ -15,10 +15,11 @@ template <int KP>
 static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaStream_t st) {
   const int d = idx->d;
   bool done = false;
-  if constexpr (KP <= 64) {
+  if constexpr (KP <= 128) {
     if (idx->kernel_now == LMI_RESCORE_TC) {
       done = true;
-      constexpr int STAGES = (KP <= 16) ? 5 : 4;
+      // 32 KB stages beside the [k' + 16][128] x 8 B candidate lists: k' = 128 (k = 100) leaves room for two
+      constexpr int STAGES = (KP <= 16) ? 5 : (KP <= 64) ? 4 : 2;
       auto kern = rescore_ts_kernel<KP, STAGES>;
       constexpr size_t smem = ts_smem_bytes<KP, STAGES>();
       static bool attr_done = false;
@@ -30,7 +31,10 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
                                                    idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
                                                    idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
       idx->rescore_name = "rescore_ts_kernel";
-    } else if (idx->kernel_now == LMI_RESCORE_TC_SS) {
+    }
+  }
+  if constexpr (KP <= 64) {
+    if (idx->kernel_now == LMI_RESCORE_TC_SS) {
       done = true;
       constexpr int STAGES = (KP <= 16) ? 4 : 3;
       auto kern = rescore_tc_kernel<KP, STAGES>;
@@ -99,8 +103,10 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
   // an empty shard has no tensor map and no work items: the (idle) CUDA-core kernel is launched instead
   int kernel = LMI_RESCORE_SIMT;
-  if (idx->rescore != LMI_RESCORE_SIMT && KP <= 64 && idx->tmap_x_ok)
-    kernel = (idx->rescore == LMI_RESCORE_TC && d <= 2 * kTsACols) ? LMI_RESCORE_TC : LMI_RESCORE_TC_SS;
+  if (idx->rescore != LMI_RESCORE_SIMT && idx->tmap_x_ok) {
+    if (idx->rescore == LMI_RESCORE_TC && d <= 2 * kTsACols) kernel = LMI_RESCORE_TC;        // k' <= 128
+    else if (KP <= 64) kernel = LMI_RESCORE_TC_SS;
+  }
   idx->kernel_now = kernel;
   const bool use_tc = (kernel == LMI_RESCORE_TC_SS);       // SS kernel: needs the bucket-ordered query copy
   if (kernel == LMI_RESCORE_TC) {

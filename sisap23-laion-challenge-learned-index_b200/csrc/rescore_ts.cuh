@@ -230,7 +230,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       for (int t = 0; t < n_tiles; ++t, ++g) {
         if ((int)(g & 1u) != parity) {             // the other warp's tile: just step over its stages
           stage += k_stages;
-          if (stage >= STAGES) { stage -= STAGES; phase ^= 1; }
+          while (stage >= STAGES) { stage -= STAGES; phase ^= 1; }   // STAGES may be smaller than a tile's stages (k' = 128)
           continue;
         }
         ptx::mbar_wait(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);

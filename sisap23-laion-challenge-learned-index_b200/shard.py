@@ -10,7 +10,9 @@ the result independent of the number of ranks.
 Host-side pieces (numpy, no GPU needed -- these are what the world_size-2 ``gloo`` tests run):
   * ``lpt_owners``      -- the bucket -> rank map, identical to the one liblmi_b200.so computes in
                            ``lmi_store_begin`` (csrc/lmi_api_store.inl: longest-processing-time on n_b^2)
-  * ``shard_keep_mask`` -- which objects a rank holds under either policy
+  * ``shard_keep_mask`` -- which objects a rank holds under each policy (whole buckets, stripes of every
+                           bucket, or caller-partitioned row ranges -- ``SHARD_RANGES``, for datasets that
+                           never exist in one piece)
   * ``merge_partials``  -- numpy mirror of ``merge_partials_kernel`` (csrc/finalize.cuh)
 Device piece:
   * ``DistributedSearch`` -- search_partial -> ``dist.all_gather_into_tensor`` (NCCL) -> merge kernel
@@ -20,6 +22,10 @@ from __future__ import annotations
 import numpy as np
 
 SHARD_BUCKETS, SHARD_STRIPES = 0, 1
+# Caller-partitioned objects: rank r is handed rows [N*r/world, N*(r+1)/world) only and builds an ordinary
+# (unsharded) index over them with id_base = first row + 1.  This is how a dataset that does not fit one
+# host or one GPU is loaded (100M x 768 fp16 = 154 GB: 19.2 GB per GPU); the exchange and merge are the same.
+SHARD_RANGES = 2
 
 # layout of one exchanged entry (csrc/common.cuh: struct Partial, 16 bytes)
 PARTIAL_DTYPE = np.dtype([("dist", "<f8"), ("id", "<u4"), ("rank", "<u4")])
@@ -51,6 +57,10 @@ def shard_keep_mask(pred_categories, n_categories, rank, world, policy=SHARD_BUC
     sizes = np.bincount(pc, minlength=n_categories).astype(np.int64)
     if policy == SHARD_BUCKETS:
         return lpt_owners(sizes, world)[pc] == rank
+    if policy == SHARD_RANGES:
+        lo, hi = range_of_rank(pc.shape[0], rank, world)
+        i = np.arange(pc.shape[0])
+        return (i >= lo) & (i < hi)
     # rank of every object inside its bucket (stable order = ascending object id)
     order = np.argsort(pc, kind="stable")
     start = np.concatenate([[0], np.cumsum(sizes)[:-1]])
@@ -59,6 +69,11 @@ def shard_keep_mask(pred_categories, n_categories, rank, world, policy=SHARD_BUC
     n = sizes[pc]
     lo, hi = n * rank // world, n * (rank + 1) // world
     return (in_bucket >= lo) & (in_bucket < hi)
+
+
+def range_of_rank(n, rank, world):
+    """Rows [lo, hi) of an N-row dataset that rank `rank` loads under SHARD_RANGES."""
+    return n * rank // world, n * (rank + 1) // world
 
 
 def pack_partials(dists, ids, ranks):

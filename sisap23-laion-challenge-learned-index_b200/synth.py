@@ -88,5 +88,33 @@ class SynthWorld:
                     queries_nav=self.project(queries))
 
 
+    # ---- chunk-seeded stream: any process can produce any row range (datasets that never exist in one piece) ----
+    def draw_range(self, lo: int, hi: int, chunk: int = 262_144) -> torch.Tensor:
+        """Rows [lo, hi) of the chunk-seeded dataset: block c (rows c*chunk ...) comes from its own
+        generator seeded by (seed_data, c), so the rows do not depend on who draws them or in what order.
+        (A different stream from ``generate()``'s sequential one.)"""
+        s = self.spec
+        out = torch.empty(hi - lo, s.d, dtype=torch.float16, device=self.device)
+        for c in range(lo // chunk, (hi + chunk - 1) // chunk):
+            gen = torch.Generator(device=self.device).manual_seed(s.seed_data * 1_000_003 + 1 + c)
+            block = self._draw(chunk, gen)                      # always a full block: the tail must not change the stream
+            b_lo, b_hi = max(lo, c * chunk), min(hi, (c + 1) * chunk)
+            out[b_lo - lo:b_hi - lo] = block[b_lo - c * chunk:b_hi - c * chunk]
+        return out
+
+    def generate_range(self, lo: int, hi: int, chunk: int = 262_144):
+        """dict(data_f16 [hi-lo,d], data_nav, queries_f16, queries_nav) for rows [lo, hi) of the chunk-seeded
+        dataset of ``spec.n`` rows; PCA is fitted on rows [0, pca_rows) by every caller identically."""
+        s = self.spec
+        self.fit_pca(self.draw_range(0, min(s.n, s.pca_rows), chunk))
+        data = self.draw_range(lo, hi, chunk)
+        nav = torch.empty(hi - lo, s.d_nav, dtype=torch.float32, device=self.device)
+        for a in range(0, hi - lo, chunk):
+            nav[a:a + chunk] = self.project(data[a:a + chunk])
+        genq = torch.Generator(device=self.device).manual_seed(s.seed_queries)
+        queries = self._draw(s.nq, genq)
+        return dict(data_f16=data, data_nav=nav, queries_f16=queries, queries_nav=self.project(queries))
+
+
 def make_synthetic(spec: SynthSpec, device="cpu"):
     return SynthWorld(spec, device).generate()

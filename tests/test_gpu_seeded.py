@@ -67,10 +67,12 @@ def test_seeded_vs_oracle(case, nb, k):
     assert (a2 == a).all() and (d2 == d).all()                              # idempotent / deterministic
 
 
-@pytest.mark.parametrize("nb,k", [(4, 10), (3, 50)])
+@pytest.mark.parametrize("nb,k", [(4, 10), (3, 50), (2, 100)])
 def test_tc_equals_simt(case, nb, k):
     c = case
-    d1, a1 = _search(_index(c, 1), c, nb, k)
+    li1 = _index(c, 1)
+    d1, a1 = _search(li1, c, nb, k)
+    assert li1.stats()["rescore_kernel"] == "rescore_ts_kernel"      # k = 100 (k' = 128) stays on tcgen05 too
     d0, a0 = _search(_index(c, 0), c, nb, k)
     assert (a1 == a0).all()
     assert (d1 == d0).all()            # same float64 refine on the same survivors -> bit-identical
@@ -156,6 +158,37 @@ def test_sharded_merge_equals_single(case, world, policy):
     gathered = torch.cat(parts)
     out = (torch.empty(nq, k, dtype=torch.float64, device="cuda"), torch.empty(nq, k, dtype=torch.int32, device="cuda"))
     keep[0].merge_partials_device(gathered, world, nq, k, out)
+    torch.cuda.synchronize()
+    assert (out[1].cpu().numpy().view(np.uint32) == ref_a).all()
+    assert (out[0].cpu().numpy() == ref_d).all()
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_presharded_ranges_equal_single(case, world):
+    """SHARD_RANGES: every rank loads only its own row range into an ordinary index (id_base = first
+    row + 1) -- the 100M layout, where no process ever holds the whole dataset.  Merged partials must
+    equal the one-GPU result bit for bit."""
+    import torch
+    from lmi_b200.index import GpuLearnedIndex
+    from lmi_b200.shard import range_of_rank
+    c = case
+    nb, k = 4, 10
+    ref_d, ref_a = _search(_index(c, 1), c, nb, k)
+    nq, n = c["queries_f16"].shape[0], c["data_f16"].shape[0]
+    qn = torch.from_numpy(c["queries_nav"]).cuda()
+    qs = torch.from_numpy(c["queries_f16"]).cuda()
+    x = torch.from_numpy(c["data_f16"]).cuda()
+    pc = torch.from_numpy(c["pred_categories"].astype(np.int64)).cuda()
+    parts, keep = [], []
+    for r in range(world):
+        lo, hi = range_of_rank(n, r, world)
+        li = GpuLearnedIndex(c["C"]).set_model(c["weights"], c["biases"])
+        li.prepare_device(x[lo:hi].contiguous(), pc[lo:hi].contiguous(), id_base=lo + 1)
+        p = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device="cuda")
+        li.search_partial_device(qn, qs, nb, k, p)
+        parts.append(p); keep.append(li)
+    out = (torch.empty(nq, k, dtype=torch.float64, device="cuda"), torch.empty(nq, k, dtype=torch.int32, device="cuda"))
+    keep[0].merge_partials_device(torch.cat(parts), world, nq, k, out)
     torch.cuda.synchronize()
     assert (out[1].cpu().numpy().view(np.uint32) == ref_a).all()
     assert (out[0].cpu().numpy() == ref_d).all()

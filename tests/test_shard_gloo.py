@@ -73,7 +73,7 @@ def _worker(rank, world, port, tag, policy, out_dir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("policy", [0, 1], ids=["buckets", "stripes"])
+@pytest.mark.parametrize("policy", [0, 1, 2], ids=["buckets", "stripes", "ranges"])
 @pytest.mark.parametrize("world", [2, 3])
 def test_sharded_protocol_matches_single_rank(tmp_path, world, policy):
     import torch.multiprocessing as mp
@@ -90,7 +90,7 @@ def test_sharded_protocol_matches_single_rank(tmp_path, world, policy):
             if policy == 0:
                 assert np.array_equal(z[f"d{nb}"], d1), f"distances differ on rank {r}, nb={nb}"
             else:
-                # stripes change the shape of the checker's BLAS products (last-ulp differences in
+                # stripes / ranges change the shape of the checker's BLAS products (last-ulp differences in
                 # numpy, not in the protocol; the CUDA path scores every pair identically)
                 np.testing.assert_allclose(z[f"d{nb}"], d1, rtol=0, atol=1e-12)
 
