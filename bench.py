@@ -416,10 +416,14 @@ def run_b200(args):
     rescore_ms = [st_loop["ms_rescore_avg"]]
     assert st_loop["n_rescore_timed"] == min(args.steps, 256), st_loop["n_rescore_timed"]
     # the same kernel launched alone after an idle gap (clocks recovered): reported beside it
-    rescore_ms_isolated = []
+    rescore_ms_isolated, mhz_isolated = [], []
     for _ in range(5):
         step()
-        rescore_ms_isolated.append(li.stats()["ms_rescore"])
+        s_ = li.stats()
+        rescore_ms_isolated.append(s_["ms_rescore"]); mhz_isolated.append(s_["k3_sm_mhz"])
+    # SM clock the kernel itself saw (clock64 / globaltimer inside the kernel): last timed step vs launched alone
+    clocks["sm_mhz_in_kernel"] = st_loop["k3_sm_mhz"]
+    clocks["sm_mhz_in_kernel_isolated"] = float(np.mean(mhz_isolated))
     st = li.stats()
 
     # ---- end to end: host buffers in, host buffers out, copies inside the timed region ----
@@ -505,14 +509,23 @@ def run_b200(args):
     # Denominator: MEASURED_PEAKS.json.  The kernel is timed inside a long step; when the clock sampler saw
     # sw_power_cap during the timed region the sustained cuBLAS figure is the comparable one (the burst
     # figure is what a kernel timed alone at 1965 MHz reaches); both fractions are reported.
-    power_capped = "sw_power_cap" in (clocks.get("reasons") or [])
+    power_capped = "sw_power_cap" in (clocks.get("reasons") or []) or \
+        0 < clocks.get("sm_mhz_in_kernel", 0) < 0.97 * (clocks.get("sm_max_mhz") or 1965.0)
     tensor_peak = peaks["tflops_sustained"] if (power_capped and peaks.get("tflops_sustained")) else peaks["tflops"]
     if t_gemm >= t_hbm:
         roof = dict(bound="tensor", achieved=flops / t_k / 1e12, peak=tensor_peak, unit="TFLOP/s")
         roof["frac_vs_burst_peak"] = roof["achieved"] / peaks["tflops"]
-        roof["peak_kind"] = "sustained (sw_power_cap active in the timed region)" if tensor_peak != peaks["tflops"] else "burst"
+        roof["peak_kind"] = ("sustained (power-capped in the timed region: sw_power_cap reported or the in-kernel SM clock "
+                             "below 97% of max)") if tensor_peak != peaks["tflops"] else "burst"
+        roof["frac_vs_sustained_peak"] = roof["achieved"] / peaks["tflops_sustained"] if peaks.get("tflops_sustained") else None
+        # share of the 128 x 64 MMA tiles' work that is real (query tiles are padded to 128 rows, object tiles to 64)
+        roof["tile_efficiency"] = st["pairs"] / st["padded_pairs"] if st.get("padded_pairs") else None
     else:
         roof = dict(bound="hbm", achieved=bytes_algo / t_k / 1e9, peak=peaks["hbm_gbs"], unit="GB/s")
+    traffic = None            # DRAM bytes per launch of the dominant kernel, from the committed ncu capture
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(st["rescore_kernel"])
     roof.update(frac=roof["achieved"] / roof["peak"], traffic=traffic, kernel=st["rescore_kernel"],
                 kernel_ms=t_k * 1e3, kernel_ms_isolated=float(np.mean(rescore_ms_isolated)),
                 kernel_share_of_step=t_k * 1e3 / ms_per_step, peak_source=peaks["source"], algorithmic_flops=flops,
@@ -539,7 +552,7 @@ def run_b200(args):
             "stages_ms": {k_: st[k_] for k_ in ("ms_navigate", "ms_plan", "ms_rescore", "ms_finalize", "ms_total")},
             "parity_sample": parity, "presharded": presharded,
             "exactness": {"n_uncertified": st["n_uncertified"], "max_abs_score_err": st["max_abs_score_err"]},
-            "store_build_seconds": store_seconds, "work_items": st["n_work_items"],
+            "store_build_seconds": store_seconds, "work_items": st["n_work_items"], "chunk_objects": st["chunk_objects"],
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -65,6 +65,9 @@ typedef struct {
    * (at most the last 256), and how many went into it; option "timing" = 1 */
   float ms_rescore_avg;
   int32_t n_rescore_timed;
+  int64_t padded_pairs;          /* sum over work items of 128 x ceil64(objects): pairs the MMA tiles compute, padding included */
+  float k3_sm_mhz;               /* SM clock during the last rescoring kernel (clock64 / globaltimer on CTA 0; tcgen05 kernel only) */
+  int32_t chunk_objects;         /* objects per work item used by the last search (option "chunk_objects", 0 = automatic) */
 } lmi_stats;
 
 const char* lmi_last_error(void);
@@ -76,7 +79,7 @@ const char* lmi_version(void);
 int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories);
 void lmi_destroy(lmi_index* idx);
 
-/* name/value tunables: "rescore" (LMI_RESCORE_*), "chunk_objects", "kprime_extra",
+/* name/value tunables: "rescore" (LMI_RESCORE_*), "chunk_objects" (0 = chosen per search), "kprime_extra",
  * "timing" (1 = record per-stage CUDA events). */
 int lmi_set_option(lmi_index* idx, const char* name, int64_t value);
 

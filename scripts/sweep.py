@@ -77,7 +77,7 @@ def main():
                            rescore_ms=t_k * 1e3, kernel=st["rescore_kernel"], bound="tensor" if t_gemm >= t_hbm else "hbm",
                            t_roof_ms=max(t_gemm, t_hbm) * 1e3, roofline_frac=max(t_gemm, t_hbm) / t_k,
                            tflops=flops / t_k / 1e12, hbm_gbs=bytes_algo / t_k / 1e9,
-                           n_uncertified=st["n_uncertified"], work_items=st["n_work_items"])
+                           n_uncertified=st["n_uncertified"], work_items=st["n_work_items"], chunk_objects=st["chunk_objects"])
                 rows.append(row)
                 fh.write(json.dumps(row) + "\n"); fh.flush()
                 print(json.dumps(row), flush=True)

@@ -30,6 +30,7 @@ class LmiStats(C.Structure):
         ("ms_navigate", C.c_float), ("ms_plan", C.c_float), ("ms_rescore", C.c_float),
         ("ms_finalize", C.c_float), ("ms_total", C.c_float),
         ("ms_rescore_avg", C.c_float), ("n_rescore_timed", C.c_int32),
+        ("padded_pairs", C.c_int64), ("k3_sm_mhz", C.c_float), ("chunk_objects", C.c_int32),
     ]
 
     def as_dict(self):

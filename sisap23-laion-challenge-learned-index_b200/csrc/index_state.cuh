@@ -51,7 +51,7 @@ struct lmi_index {
 
   // options
   int rescore = LMI_RESCORE_TC;
-  int chunk_objects = 8192;
+  int chunk_objects = 0;                    // objects per work item; 0 = chosen per search (choose_chunk)
   int kprime_extra = 6;
   int timing = 1;
   int dbg_flags = 0;                        // experiments only (bit 0: rescoring kernel never inserts)
@@ -72,8 +72,10 @@ struct lmi_index {
   float* inv_norm = nullptr;                // [n_local]
   uint32_t* ids = nullptr;                  // [n_local]
   std::vector<int64_t> h_bucket_ptr;        // [C+1] local CSR (host copy)
-  std::vector<int64_t> h_chunks_sorted_prefix;   // prefix sums of chunks_b sorted descending
-  int64_t total_chunks = 0, max_chunks = 0;
+  std::vector<int64_t> h_sizes_sorted;      // local bucket sizes, descending (workspace bounds for any chunk size)
+  int64_t n_nonempty = 0;                   // local buckets holding objects
+  double pair_fraction = 1.0;               // expected share of (query, bucket) pairs that hit a locally non-empty bucket
+  int chunk_now = 0;                        // chunk size of the last search (stats)
   CUtensorMap tmap_x{};                     // store tensor map, box 256 x 64 (SS kernel)
   CUtensorMap tmap_x64{};                   // store tensor map, box 64 x 64 (TS kernel)
   CUtensorMap tmap_xpf{};                   // store tensor map, box 64 x 256 unswizzled (TS kernel, L2 prefetch)

@@ -116,8 +116,7 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
       return set_error(LMI_ERR_ARG, "rescore: 0 (simt), 1 (tcgen05, queries in TMEM) or 2 (tcgen05, smem operands)");
     idx->rescore = (int)value;
   } else if (n == "chunk_objects") {
-    if (value < 256 || value > (1 << 24)) return set_error(LMI_ERR_ARG, "chunk_objects out of range");
-    if (idx->has_store || idx->store_open) return set_error(LMI_ERR_STATE, "chunk_objects must be set before the store is built");
+    if (value != 0 && (value < 256 || value > (1 << 24))) return set_error(LMI_ERR_ARG, "chunk_objects out of range (0 = automatic)");
     idx->chunk_objects = (int)((value + 255) / 256 * 256);
   } else if (n == "kprime_extra") {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");

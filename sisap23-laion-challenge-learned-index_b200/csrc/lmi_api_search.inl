@@ -66,6 +66,23 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
   return LMI_OK;
 }
 
+// Objects per work item.  Small chunks balance the persistent grid; large chunks let a row's candidate
+// list live longer (fewer insertions: a list that has seen n objects admits ~k'/n of the next ones, and
+// every chunk starts a new list) and leave fewer partial lists to merge.  Measured on 10M / nb = 4
+// (profiles/r1_chunk_sweep.txt): k = 10 is best around 32k objects (1,200 work-list entries on 74
+// clusters), k = 100 -- where insertions dominate -- at 64k.  So: aim at ~13 (k' <= 32) or ~8 entries per
+// cluster, from the expected number of query tiles on this shard.
+static int choose_chunk(const lmi_index* idx, int64_t nq, int nb, int KP) {
+  if (idx->chunk_objects > 0) return idx->chunk_objects;
+  const double clusters = std::max(1, idx->num_sms / 2);
+  const double target = clusters * (KP >= 64 ? 8.0 : 13.0);
+  const double qtiles = (double)nq * nb * idx->pair_fraction / kTileQ + 0.5 * (double)idx->n_nonempty;
+  const double avg_bucket = (double)idx->n_local / (double)std::max<int64_t>(idx->n_nonempty, 1);
+  double c = qtiles * avg_bucket / target;
+  c = std::min(std::max(c, 1024.0), (double)(1 << 22));
+  return (int)(((int64_t)c + 255) / 256 * 256);
+}
+
 // The whole hot path on `st`.  Exactly one of q_nav_dev / cls64_dev is used to obtain the bucket
 // list: navigation (search) or caller-supplied categories (search_rank, nb = 1).
 static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls64_dev, const uint16_t* q16_dev,
@@ -93,13 +110,22 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(idx->pair_slot.reserve((size_t)n_pairs * 4));
   LMI_CUDA(idx->scalars.reserve(sizeof(PlanScalars)));
   const int64_t qtiles_max = (nq + kTileQ - 1) / kTileQ;
+  const int chunk = choose_chunk(idx, nq, nb, KP);
+  idx->chunk_now = chunk;
+  int64_t total_chunks = 0, max_chunks = 0, top_nb_chunks = 0;         // h_sizes_sorted is descending
+  for (int c = 0; c < C; ++c) {
+    const int64_t ch = (idx->h_sizes_sorted[c] + chunk - 1) / chunk;
+    total_chunks += ch;
+    if (c == 0) max_chunks = ch;
+    if (c < nb) top_nb_chunks += ch;
+  }
   // entries: at most qtiles_b * chunks_b + 1 (dummy) per bucket
-  const int64_t items_a = qtiles_max * idx->total_chunks + C;
-  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(idx->max_chunks, 1) + C;
+  const int64_t items_a = qtiles_max * total_chunks + C;
+  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(max_chunks, 1) + C;
   const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
   if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
-  const int64_t max_plists = std::max<int64_t>(1, nq * idx->h_chunks_sorted_prefix[std::min(nb, C)]);
+  const int64_t max_plists = std::max<int64_t>(1, nq * top_nb_chunks);
   LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
   // an empty shard has no tensor map and no work items: the (idle) CUDA-core kernel is launched instead
   int kernel = LMI_RESCORE_SIMT;
@@ -138,7 +164,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   // ---- K2 plan ----
   LMI_CUDA(cudaMemsetAsync(idx->m_b.p, 0, (size_t)C * 4, st));
   plan_count_kernel<<<idx->num_sms * 2, 256, 0, st>>>(top, n_pairs, C, idx->m_b.as<int32_t>());
-  plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, idx->chunk_objects,
+  plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, chunk,
                                         idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
                                         idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>());
   plan_scatter_kernel<<<C, 256, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
@@ -170,6 +196,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(cudaMemcpyAsync(idx->h_scalars, idx->scalars.p, sizeof(PlanScalars), cudaMemcpyDeviceToHost, st));
   idx->stats.nq = (int32_t)nq; idx->stats.n_buckets = nb; idx->stats.k = k; idx->stats.kprime = KP;
   idx->stats.n_objects_local = idx->n_local;
+  idx->stats.chunk_objects = chunk;
   idx->last_stream = st;
   idx->stats_pending = true;
   return LMI_OK;
@@ -298,6 +325,8 @@ int lmi_get_stats(lmi_index* idx, lmi_stats* out) {
     idx->stats.pairs = s.pairs;
     idx->stats.bucket_bytes = s.bucket_objs * idx->d * 2;
     idx->stats.n_partial_lists = s.n_plists;
+    idx->stats.padded_pairs = s.padded_pairs;
+    idx->stats.k3_sm_mhz = s.k3_ns ? (float)((double)s.k3_clk * 1e3 / (double)s.k3_ns) : 0.f;
     idx->stats.n_uncertified = (int64_t)s.n_uncertified;
     double e; unsigned long long bits = s.max_err_bits; memcpy(&e, &bits, 8);
     idx->stats.max_abs_score_err = e;

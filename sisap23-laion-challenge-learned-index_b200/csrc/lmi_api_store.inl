@@ -79,18 +79,17 @@ int lmi_store_begin(lmi_index* idx, const int64_t* pred_categories, int64_t n_to
   LMI_CUDA(cudaMalloc(&idx->x, rows_alloc * idx->d * 2));
   LMI_CUDA(cudaMalloc(&idx->inv_norm, rows_alloc * 4));
   LMI_CUDA(cudaMalloc(&idx->ids, rows_alloc * 4));
-  // chunk bookkeeping for workspace bounds
-  std::vector<int64_t> chunks(C);
-  idx->total_chunks = 0; idx->max_chunks = 0;
+  // bucket-size bookkeeping for per-search workspace bounds and the chunk-size choice
+  idx->h_sizes_sorted.assign(C, 0);
+  idx->n_nonempty = 0;
+  int64_t global_of_local = 0;                     // global size of the buckets this shard holds part of
   for (int c = 0; c < C; ++c) {
     const int64_t n = idx->h_bucket_ptr[c + 1] - idx->h_bucket_ptr[c];
-    chunks[c] = (n + idx->chunk_objects - 1) / idx->chunk_objects;
-    idx->total_chunks += chunks[c];
-    idx->max_chunks = std::max(idx->max_chunks, chunks[c]);
+    idx->h_sizes_sorted[c] = n;
+    if (n > 0) { ++idx->n_nonempty; global_of_local += sizes[c]; }
   }
-  std::sort(chunks.begin(), chunks.end(), [](int64_t a, int64_t b) { return a > b; });
-  idx->h_chunks_sorted_prefix.assign(C + 1, 0);
-  for (int c = 0; c < C; ++c) idx->h_chunks_sorted_prefix[c + 1] = idx->h_chunks_sorted_prefix[c] + chunks[c];
+  idx->pair_fraction = n_total > 0 ? (double)global_of_local / (double)n_total : 1.0;
+  std::sort(idx->h_sizes_sorted.begin(), idx->h_sizes_sorted.end(), [](int64_t a, int64_t b) { return a > b; });
   idx->store_open = true;
   return LMI_OK;
 }

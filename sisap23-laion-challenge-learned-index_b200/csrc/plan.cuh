@@ -20,6 +20,9 @@ struct PlanScalars {          // device-resident scalars of one search
   unsigned long long max_err_bits;   // float64 bits of max |cos32-cos64| (atomicMax on non-negative doubles)
   int32_t work_counter;       // dynamic scheduler cursor
   int32_t pad;
+  int64_t padded_pairs;       // sum over items of 128 x ceil64(objects): what the 128 x 64 MMA tiles really compute
+  unsigned long long k3_clk;  // rescoring kernel, CTA 0: SM cycles (clock64) and nanoseconds (globaltimer) from
+  unsigned long long k3_ns;   //   start to end -> the SM clock the kernel actually ran at
 };
 
 // m_b histogram.  top_cls: int32 [nq*nb]; entries outside [0,C) are ignored.
@@ -44,7 +47,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
   __shared__ long long s_carry[3];
   const int tid = threadIdx.x;
   if (tid < 3) s_carry[tid] = 0;
-  long long tot_pairs = 0, tot_objs = 0;
+  long long tot_pairs = 0, tot_objs = 0, tot_padded = 0;
   __syncthreads();
   // three running exclusive scans, processed in blocks of 1024 buckets:
   //   0: slots (m_b)   1: items (qtiles*chunks)   2: plists (m_b*chunks)
@@ -59,6 +62,10 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       chunks_b[b] = (int)ch;
       tot_pairs += m * nobj;
       if (m > 0) tot_objs += nobj;
+      if (ch > 0) {
+        const long long last = nobj - (ch - 1) * chunk;
+        tot_padded += qt * kTileQ * ((ch - 1) * ((chunk + 63) / 64 * 64) + (last + 63) / 64 * 64);
+      }
     }
     // work list entries come in PAIRS (entries 2i, 2i+1 = one item of a 2-CTA cluster of the
     // TMEM-resident rescoring kernel; the other kernels treat every entry as an independent item):
@@ -126,6 +133,11 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
   for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
   const long long pairs = s_scan[0];
   __syncthreads();
+  s_scan[tid] = tot_padded;
+  __syncthreads();
+  for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
+  const long long padded = s_scan[0];
+  __syncthreads();
   s_scan[tid] = tot_objs;
   __syncthreads();
   for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
@@ -139,6 +151,9 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
     sc->n_uncertified = 0ull;
     sc->max_err_bits = 0ull;
     sc->work_counter = 0;
+    sc->padded_pairs = padded;
+    sc->k3_clk = 0ull;
+    sc->k3_ns = 0ull;
   }
 }
 

@@ -128,6 +128,9 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const uint32_t tmem_d = tmem_base + kTsACols;
+  // CTA 0 reports the SM clock the kernel really ran at (cycles / nanoseconds between here and the end)
+  long long clk0 = 0; unsigned long long ns0 = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { clk0 = clock64(); ns0 = ptx::globaltimer_ns(); }
 
   // every consumer warp: next pair index from the ring, then release the slot to the leader
   const uint32_t iempty_leader = ptx::mapa(ptx::smem_u32(iempty_bar), 0);
@@ -228,9 +231,21 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);             // this item's queries are in TMEM
       a_phase ^= 1;
       for (int t = 0; t < n_tiles; ++t, ++g) {
-        if ((int)(g & 1u) != parity) {             // the other warp's tile: just step over its stages
-          stage += k_stages;
-          while (stage >= STAGES) { stage -= STAGES; phase ^= 1; }   // STAGES may be smaller than a tile's stages (k' = 128)
+        if ((int)(g & 1u) != parity) {             // the other warp's tile: step over its stages
+          if constexpr (STAGES >= 4) {
+            // ring longer than a tile: when this warp later waits on a stage, the stage's previous
+            // phase is complete by construction (its refill needed that phase consumed)
+            stage += k_stages;
+            if (stage >= STAGES) { stage -= STAGES; phase ^= 1; }
+          } else {
+            // short ring (k' = 128 leaves room for two stages): a stage comes round again inside one
+            // tile, and a parity wait for phase n+1 passes at once while the barrier is still in
+            // phase n -- so observe every phase of the skipped stages instead of counting them
+            for (int ks = 0; ks < k_stages; ++ks) {
+              ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
           continue;
         }
         ptx::mbar_wait(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);
@@ -392,6 +407,10 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    sc->k3_clk = (unsigned long long)(clock64() - clk0);
+    sc->k3_ns = ptx::globaltimer_ns() - ns0;
+  }
   ptx::cluster_sync();                               // no CTA exits while the peer may still signal it
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc<512>(tmem_base); }
 }

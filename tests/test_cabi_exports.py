@@ -33,8 +33,8 @@ def test_version_and_error_string(lib):
 
 def test_stats_struct_matches_header():
     from lmi_b200._lib import LmiStats
-    # 4*int32 + 6*int64 + double + 6*float + int32 (+4 pad) = 16 + 48 + 8 + 24 + 4 + 4
-    assert ctypes.sizeof(LmiStats) == 104
+    # 4*int32 + 6*int64 + double + 6*float + int32 (+4 pad) + int64 + 2*float = 16 + 48 + 8 + 24 + 4 + 4 + 8 + 8
+    assert ctypes.sizeof(LmiStats) == 120
 
 
 def test_sass_is_blackwell_native():
