@@ -36,7 +36,8 @@ def parse_args():
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    p.add_argument("--n", type=int, default=10_000_000)
+    # "--rows" is the spelling to use behind torchrun, whose own parser would claim "--n" as an abbreviation
+    p.add_argument("--n", "--rows", dest="n", type=int, default=10_000_000)
     p.add_argument("--nq", type=int, default=10_000)
     p.add_argument("--categories", type=int, default=122)
     p.add_argument("--buckets", type=int, default=4)
@@ -289,6 +290,14 @@ def cpu_reference_sample(inp, args, target_seconds, classes=None):
     extrapolation is faithful; the sample is described in the returned dict."""
     import torch
     from oracle import lmi_oracle as O
+    # all host threads, whatever the launcher exported (torchrun sets OMP_NUM_THREADS=1 for its workers)
+    n_host = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=n_host)
+    except Exception:
+        pass
+    torch.set_num_threads(n_host)
     t0 = time.time()
     q_nav = inp["queries_nav"].cpu().numpy()
     q16 = inp["queries_f16"].cpu().numpy()
