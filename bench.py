@@ -435,6 +435,33 @@ def run_b200(args):
     clocks["sm_mhz_in_kernel_isolated"] = float(np.mean(mhz_isolated))
     st = li.stats()
 
+    # ---- N > 1: where a sharded step spends its time (diagnostic pass, not part of `value`) ----
+    shard_breakdown = None
+    if world > 1:
+        nbytes = li.partial_bytes(nq, k)
+        part = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        gathered = torch.empty(world * nbytes, dtype=torch.uint8, device=device)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        acc = np.zeros(3)
+        reps = 10
+        for _ in range(reps):
+            barrier()
+            evs[0].record(); li.search_partial_device(qn, qs, nb, k, part)
+            evs[1].record(); dist.all_gather_into_tensor(gathered, part)
+            evs[2].record(); li.merge_partials_device(gathered, world, nq, k, out)
+            evs[3].record(); torch.cuda.synchronize()
+            acc += [evs[i].elapsed_time(evs[i + 1]) for i in range(3)]
+        mine = torch.tensor(list(acc / reps) + [st_loop["ms_rescore_avg"]], device=device, dtype=torch.float64)
+        allr = torch.empty(world, 4, device=device, dtype=torch.float64)
+        dist.all_gather_into_tensor(allr, mine)
+        allr = allr.cpu().numpy()
+        shard_breakdown = dict(partial_search_ms_per_rank=[round(float(v), 4) for v in allr[:, 0]],
+                               all_gather_ms_max=float(allr[:, 1].max()), all_gather_ms_min=float(allr[:, 1].min()),
+                               merge_ms_max=float(allr[:, 2].max()),
+                               rescore_ms_per_rank=[round(float(v), 4) for v in allr[:, 3]],
+                               note="ranks start each repetition together (barrier); the all-gather time of a rank includes "
+                                    "waiting for the slowest rank's partial search")
+
     # ---- end to end: host buffers in, host buffers out, copies inside the timed region ----
     # N=1: the reference-facing C-ABI call lmi_search (pinned host inputs; H2D, search, D2H inside the call).
     # N>1: every rank uploads the (replicated) queries from pinned host memory, runs the sharded step and
@@ -559,7 +586,7 @@ def run_b200(args):
             "e2e": e2e, "gpu_launches": args.steps * (7 + (1 if world > 1 else 0)),   # nav, 4 plan kernels, rescoring, finalize (+ merge)
             "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "stages_ms": {k_: st[k_] for k_ in ("ms_navigate", "ms_plan", "ms_rescore", "ms_finalize", "ms_total")},
-            "parity_sample": parity, "presharded": presharded,
+            "parity_sample": parity, "presharded": presharded, "shard_breakdown": shard_breakdown,
             "exactness": {"n_uncertified": st["n_uncertified"], "max_abs_score_err": st["max_abs_score_err"]},
             "store_build_seconds": store_seconds, "work_items": st["n_work_items"], "chunk_objects": st["chunk_objects"],
         }

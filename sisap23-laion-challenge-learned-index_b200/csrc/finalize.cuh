@@ -19,6 +19,8 @@
 namespace lmi {
 
 constexpr int kFinWarps = 8;
+constexpr int kFinRegE = 8;           // entries per lane of the register-resident selection (<= 256 entries per query)
+constexpr int kFinMaxVec = 128;       // uint4 per row, d <= 1024
 constexpr double kCertEps = 2e-5;       // bound used by the exactness certificate
 
 __device__ __forceinline__ bool key_less(double da, uint32_t ra, uint32_t ia, int ga,
@@ -46,6 +48,7 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   __shared__ double s_dist[kFinWarps][kMaxKPrime];
   __shared__ int64_t s_rbeg[kFinWarps][32];     // per rank: first entry (global Cand index)
   __shared__ int32_t s_rcum[kFinWarps][33];     // per rank: cumulative entry count
+  __shared__ uint4 s_q[kFinWarps][kFinMaxVec];  // the query row (fp16 bits)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t qi = (int64_t)blockIdx.x * kFinWarps + warp;
@@ -84,59 +87,112 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
     __syncwarp();
   };
 
+  // Fast path (the usual case: one rank group and at most 32 x kFinRegE entries, e.g. 4 ranks x 3 chunks
+  // x k' = 16): every lane reads its entries once and the R rounds run on registers.
+  bool fast = (n_groups == 1);
+  if (fast) {
+    load_ranges(0);
+    fast = s_rcum[warp][nb] <= 32 * kFinRegE;
+  }
+  if (fast) {
+    const int total = s_rcum[warp][nb];
+    float es[kFinRegE]; int32_t ep[kFinRegE]; int er[kFinRegE];
+#pragma unroll
+    for (int u = 0; u < kFinRegE; ++u) {
+      const int g = lane + 32 * u;                 // entry number in (rank, list, position) order
+      es[u] = kNegInf * 2.f; ep[u] = -1; er[u] = 0;
+      if (g < total) {
+        int r = 0;
+        while (g >= s_rcum[warp][r + 1]) ++r;
+        const Cand c = plists[s_rbeg[warp][r] + (g - s_rcum[warp][r])];
+        if (c.pos >= 0) { es[u] = c.score; ep[u] = c.pos; er[u] = r; }
+      }
+    }
+    for (int t = 0; t < R; ++t) {
+      // per lane: best remaining entry with its payload (select chains only: the arrays stay in registers)
+      float best_s = kNegInf * 2.f; int best_g = 0x7fffffff; int32_t best_p = -1; int best_r = 0;
+#pragma unroll
+      for (int u = 0; u < kFinRegE; ++u) {         // ascending g per lane: strict '>' keeps the lowest g of equal scores
+        const bool better = ep[u] >= 0 && es[u] > best_s;
+        best_s = better ? es[u] : best_s;
+        best_g = better ? lane + 32 * u : best_g;
+        best_p = better ? ep[u] : best_p;
+        best_r = better ? er[u] : best_r;
+      }
+      float win_s = best_s; int win_g = best_g;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float os = __shfl_xor_sync(0xffffffffu, win_s, o);
+        const int og = __shfl_xor_sync(0xffffffffu, win_g, o);
+        if (os > win_s || (os == win_s && og < win_g)) { win_s = os; win_g = og; }
+      }
+      if (win_g == 0x7fffffff) break;              // no more valid entries (warp-uniform)
+      if (win_g == best_g) {                       // exactly one lane
+        s_pos[warp][t] = best_p; s_rank[warp][t] = (uint32_t)best_r; s_dist[warp][t] = (double)best_s;
+      }
+#pragma unroll
+      for (int u = 0; u < kFinRegE; ++u) ep[u] = (lane + 32 * u == win_g) ? -1 : ep[u];     // taken
+      n_sel = t + 1;
+    }
+  } else {
   for (int t = 0; t < R; ++t) {
-    float best_s = kNegInf * 2.f;      // -inf
-    long long best_g = 0x7fffffffffffffffLL;
-    int32_t best_pos = -1;
-    uint32_t best_rank = 0;
-    long long gbase = 0;
-    for (int grp = 0; grp < n_groups; ++grp) {
-      if (n_groups > 1 || t == 0) load_ranges(grp);     // one group (nb <= 32): ranges loaded once
-      __syncwarp();
-      const int nr = min(32, nb - grp * 32);
-      const int total = s_rcum[warp][nr];
-      for (int r = 0; r < nr; ++r) {
-        const int c0 = s_rcum[warp][r], c1 = s_rcum[warp][r + 1];
-        const Cand* base = plists + s_rbeg[warp][r];
-        for (int j = lane; j < c1 - c0; j += 32) {
-          const Cand c = base[j];
-          if (c.pos < 0) continue;
-          const long long g = gbase + c0 + j;
-          const bool after_prev = (c.score < prev_s) || (c.score == prev_s && g > prev_g);
-          if (!after_prev) continue;
-          if (c.score > best_s || (c.score == best_s && g < best_g)) {
-            best_s = c.score; best_g = g; best_pos = c.pos; best_rank = (uint32_t)(grp * 32 + r);
+      float best_s = kNegInf * 2.f;      // -inf
+      long long best_g = 0x7fffffffffffffffLL;
+      int32_t best_pos = -1;
+      uint32_t best_rank = 0;
+      long long gbase = 0;
+      for (int grp = 0; grp < n_groups; ++grp) {
+        if (n_groups > 1 || t == 0) load_ranges(grp);     // one group (nb <= 32): ranges loaded once
+        __syncwarp();
+        const int nr = min(32, nb - grp * 32);
+        const int total = s_rcum[warp][nr];
+        for (int r = 0; r < nr; ++r) {
+          const int c0 = s_rcum[warp][r], c1 = s_rcum[warp][r + 1];
+          const Cand* base = plists + s_rbeg[warp][r];
+          for (int j = lane; j < c1 - c0; j += 32) {
+            const Cand c = base[j];
+            if (c.pos < 0) continue;
+            const long long g = gbase + c0 + j;
+            const bool after_prev = (c.score < prev_s) || (c.score == prev_s && g > prev_g);
+            if (!after_prev) continue;
+            if (c.score > best_s || (c.score == best_s && g < best_g)) {
+              best_s = c.score; best_g = g; best_pos = c.pos; best_rank = (uint32_t)(grp * 32 + r);
+            }
           }
         }
+        gbase += total;
       }
-      gbase += total;
+      // warp arg-max by (score desc, g asc)
+  #pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float os = __shfl_xor_sync(0xffffffffu, best_s, o);
+        const long long og = __shfl_xor_sync(0xffffffffu, best_g, o);
+        const int32_t op = __shfl_xor_sync(0xffffffffu, best_pos, o);
+        const uint32_t orr = __shfl_xor_sync(0xffffffffu, best_rank, o);
+        if (os > best_s || (os == best_s && og < best_g)) { best_s = os; best_g = og; best_pos = op; best_rank = orr; }
+      }
+      if (best_pos < 0) break;           // no more valid entries (warp-uniform)
+      if (lane == 0) {
+        s_pos[warp][t] = best_pos;
+        s_rank[warp][t] = best_rank;
+        s_dist[warp][t] = (double)best_s;   // temporarily the fp32 score
+      }
+      prev_s = best_s; prev_g = best_g;
+      n_sel = t + 1;
     }
-    // warp arg-max by (score desc, g asc)
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float os = __shfl_xor_sync(0xffffffffu, best_s, o);
-      const long long og = __shfl_xor_sync(0xffffffffu, best_g, o);
-      const int32_t op = __shfl_xor_sync(0xffffffffu, best_pos, o);
-      const uint32_t orr = __shfl_xor_sync(0xffffffffu, best_rank, o);
-      if (os > best_s || (os == best_s && og < best_g)) { best_s = os; best_g = og; best_pos = op; best_rank = orr; }
-    }
-    if (best_pos < 0) break;           // no more valid entries (warp-uniform)
-    if (lane == 0) {
-      s_pos[warp][t] = best_pos;
-      s_rank[warp][t] = best_rank;
-      s_dist[warp][t] = (double)best_s;   // temporarily the fp32 score
-    }
-    prev_s = best_s; prev_g = best_g;
-    n_sel = t + 1;
-  }
+}
   __syncwarp();
 
   // ---- float64 re-scoring of the survivors ---------------------------------------------------
-  const int vec = d / 8;                                  // uint4 per row
+  // The candidate rows are random 1.5 KB reads from HBM: 4 candidates are in flight per warp (8 lanes
+  // each, 6 x 16 bytes per lane outstanding) instead of one after the other.
+  const int vec = d / 8;                                  // uint4 per row (d is a multiple of 64)
   const uint4* qrow = reinterpret_cast<const uint4*>(q + (size_t)qi * d);
+  uint4* sq = s_q[warp];
   double qq = 0.0;
   for (int v = lane; v < vec; v += 32) {
     const uint4 u = qrow[v];
+    sq[v] = u;
     const __half2* h = reinterpret_cast<const __half2*>(&u);
 #pragma unroll
     for (int j = 0; j < 4; ++j) { const float2 f = __half22float2(h[j]); qq += (double)f.x * f.x + (double)f.y * f.y; }
@@ -144,34 +200,50 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   qq = warp_sum(qq);
   const double qn = (qq == 0.0) ? 1.0 : sqrt(qq);
   double max_err = 0.0;
-  float score_R = 0.f;
-  for (int t = 0; t < n_sel; ++t) {
-    const int32_t pos = s_pos[warp][t];
+  const float score_R = (n_sel == R) ? (float)s_dist[warp][R - 1] : 0.f;     // before the scores are overwritten
+  __syncwarp();
+  const int grp = lane >> 3, sub = lane & 7;
+  constexpr int kUn = 6;
+  for (int t0 = 0; t0 < n_sel; t0 += 4) {
+    const int t = t0 + grp;
+    const bool valid = t < n_sel;
+    const int32_t pos = s_pos[warp][valid ? t : t0];
     const uint4* xrow = reinterpret_cast<const uint4*>(store + (size_t)pos * d);
     double dot = 0.0, xx = 0.0;
-    for (int v = lane; v < vec; v += 32) {
-      const uint4 ux = xrow[v];
-      const uint4 uq = qrow[v];
-      const __half2* hx = reinterpret_cast<const __half2*>(&ux);
-      const __half2* hq = reinterpret_cast<const __half2*>(&uq);
+    for (int v0 = sub; v0 < vec; v0 += 8 * kUn) {
+      uint4 ux[kUn];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 fx = __half22float2(hx[j]);
-        const float2 fq = __half22float2(hq[j]);
-        dot += (double)fx.x * (double)fq.x + (double)fx.y * (double)fq.y;
-        xx += (double)fx.x * (double)fx.x + (double)fx.y * (double)fx.y;
+      for (int u = 0; u < kUn; ++u) { const int v = v0 + 8 * u; ux[u] = (v < vec) ? __ldg(xrow + v) : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+      for (int u = 0; u < kUn; ++u) {
+        const int v = v0 + 8 * u;
+        if (v < vec) {
+          const uint4 uq = sq[v];
+          const __half2* hx = reinterpret_cast<const __half2*>(&ux[u]);
+          const __half2* hq = reinterpret_cast<const __half2*>(&uq);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 fx = __half22float2(hx[j]);
+            const float2 fq = __half22float2(hq[j]);
+            dot += (double)fx.x * (double)fq.x + (double)fx.y * (double)fq.y;
+            xx += (double)fx.x * (double)fx.x + (double)fx.y * (double)fx.y;
+          }
+        }
       }
     }
-    dot = warp_sum(dot);
-    xx = warp_sum(xx);
-    const double xn = (xx == 0.0) ? 1.0 : sqrt(xx);
-    const double cos64 = dot / (qn * xn);
-    const float sc32 = (float)s_dist[warp][t];
-    const double cos32 = (double)sc32 / qn;
-    max_err = fmax(max_err, fabs(cos32 - cos64));
-    if (t == R - 1) score_R = sc32;
-    __syncwarp();
-    if (lane == 0) { s_dist[warp][t] = 1.0 - cos64; s_id[warp][t] = ids[pos]; }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {                     // sum over the 8 lanes of the group
+      dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      xx += __shfl_xor_sync(0xffffffffu, xx, o);
+    }
+    if (valid && sub == 0) {
+      const double xn = (xx == 0.0) ? 1.0 : sqrt(xx);
+      const double cos64 = dot / (qn * xn);
+      const double cos32 = (double)(float)s_dist[warp][t] / qn;
+      max_err = fmax(max_err, fabs(cos32 - cos64));
+      s_dist[warp][t] = 1.0 - cos64;
+      s_id[warp][t] = ids[pos];
+    }
   }
   __syncwarp();
 
@@ -216,7 +288,9 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
       const double cos_kth = 1.0 - kth_dist;     // kth_dist = 10000 if fewer than k results -> uncertified
       if (!(cos_dropped < cos_kth)) atomicAdd(&sc->n_uncertified, 1ull);
     }
-    atomicMax(&sc->max_err_bits, (unsigned long long)__double_as_longlong(max_err));
+    // 10k same-address atomics serialise in L2 (~0.15 ms per search): only a new maximum goes there
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(max_err);
+    if (bits > __ldcg(&sc->max_err_bits)) atomicMax(&sc->max_err_bits, bits);
   }
 }
 

@@ -5,18 +5,21 @@
 // logits).  Arithmetic is plain fp32 FFMA (no TF32, no tensor cores) so bucket order matches
 // the reference's torch fp32 model up to summation order.
 //
-// One CTA = 32 queries.  Activations live in shared memory transposed ([feature][query]) so a
-// thread that owns 8 queries x 2 outputs reads its 8 activations with two broadcast LDS.128;
-// weights are stored transposed on the device ([in][out]) so a warp reads 32 consecutive
-// outputs of one input feature as a single 128-byte line (L2 resident: <= a few 100 KB).
+// One CTA = 16 queries (128 threads).  Activations live in shared memory transposed ([feature][query]) so a
+// thread that owns 8 queries x 4 outputs reads its 8 activations with two broadcast LDS.128;
+// weights are stored transposed on the device ([in][out]) and streamed through shared memory in
+// tiles of 8 input rows x 256 outputs, the next tile's loads in flight while one is consumed.
 #pragma once
 #include "common.cuh"
 
 namespace lmi {
 
-constexpr int kNavTQ = 32;          // queries per CTA
-constexpr int kNavThreads = 256;
+constexpr int kNavTQ = 16;          // queries per CTA (10k queries = 625 CTAs, 4 per SM: small CTAs balance the 148 SMs)
+constexpr int kNavThreads = 128;
 constexpr int kNavMaxLayers = 8;
+constexpr int kNavKT = 8;           // input rows per weight tile
+constexpr int kNavRegC = 8;          // classes per lane kept in registers by the top-n select (C <= 256)
+constexpr int kNavOB = 256;         // outputs per block (4 per thread)
 
 struct NavLayers {
   int n_layers;
@@ -27,8 +30,30 @@ struct NavLayers {
   int max_width;                     // max over all in/out dims
 };
 
+// One weight tile (rows x 256 outputs in shared memory) into a thread's 8 queries x NU*1 outputs.
+// Straight-line code: NU (output groups of 64 in use) and FULL (all kNavKT rows) are compile-time.
+template <int NU, bool FULL>
+__device__ __forceinline__ void nav_tile_fma(float (&acc)[4][8], const float* __restrict__ w,
+                                             const float4* __restrict__ a, int rows) {
+#pragma unroll
+  for (int r = 0; r < kNavKT; ++r) {
+    if (FULL || r < rows) {
+      const float4 lo = a[r * (kNavTQ / 4)];
+      const float4 hi = a[r * (kNavTQ / 4) + 1];
+#pragma unroll
+      for (int u = 0; u < NU; ++u) {
+        const float wv = w[r * kNavOB + 64 * u];
+        acc[u][0] = fmaf(lo.x, wv, acc[u][0]); acc[u][1] = fmaf(lo.y, wv, acc[u][1]);
+        acc[u][2] = fmaf(lo.z, wv, acc[u][2]); acc[u][3] = fmaf(lo.w, wv, acc[u][3]);
+        acc[u][4] = fmaf(hi.x, wv, acc[u][4]); acc[u][5] = fmaf(hi.y, wv, acc[u][5]);
+        acc[u][6] = fmaf(hi.z, wv, acc[u][6]); acc[u][7] = fmaf(hi.w, wv, acc[u][7]);
+      }
+    }
+  }
+}
+
 // x: [n, d_nav] fp32.  out_classes: int32 [n, n_top]; out_probs: fp32 [n, n_top] or nullptr.
-__global__ void __launch_bounds__(kNavThreads, 2)
+__global__ void __launch_bounds__(kNavThreads, 4)
 nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
            int32_t* __restrict__ out_classes, float* __restrict__ out_probs) {
   extern __shared__ float nav_smem[];
@@ -46,53 +71,95 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
   }
   __syncthreads();
 
+  // Layers.  Weights are streamed through shared memory in tiles of kNavKT input rows x 256 outputs
+  // (next tile's global loads in flight while the current one is consumed): reading them straight from
+  // L2 inside the FFMA loop left the kernel waiting ~1,900 cycles per 4 input features (ncu, round 1).
+  // A thread owns 8 queries x 4 outputs (og, og+64, og+128, og+192 of the current 256-output block);
+  // every accumulator starts from the bias and adds input features in ascending order.
   const int og = tid & 63;           // output lane
   const int qg = tid >> 6;           // query group: queries qg*8 .. qg*8+7
   float* cur = act_a;
   float* nxt = act_b;
+  float* wtile = nav_smem + (size_t)2 * L.max_width * kNavTQ;       // [2][kNavKT][kNavOB]
   for (int l = 0; l < L.n_layers; ++l) {
     const int I = L.in_dim[l], O = L.out_dim[l];
     const float* __restrict__ wt = L.wt[l];
     const float* __restrict__ bias = L.bias[l];
     const bool relu = (l + 1 < L.n_layers);
-    for (int o = og; o < O; o += 128) {
-      const int o1 = o + 64;
-      const bool has1 = o1 < O;
-      float acc0[8], acc1[8];
-      const float b0 = bias[o], b1 = has1 ? bias[o1] : 0.f;
+    const int n_tiles = (I + kNavKT - 1) / kNavKT;
+    for (int ob = 0; ob < O; ob += kNavOB) {
+      const int ncols = min(kNavOB, O - ob);
+      const int nu = (ncols + 63) / 64;                    // output groups of 64 in use (warp-uniform)
+      float acc[4][8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { acc0[j] = b0; acc1[j] = b1; }
+      for (int u = 0; u < 4; ++u) {
+        const int o = ob + og + 64 * u;
+        const float bv = (o < O) ? bias[o] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[u][j] = bv;
+      }
+      constexpr int kCols = kNavOB / kNavThreads;          // tile columns per thread
+      float wreg[kNavKT][kCols];
+      auto fetch = [&](int t) {              // a row of the tile is kNavOB consecutive floats: coalesced
+#pragma unroll
+        for (int r = 0; r < kNavKT; ++r) {
+          const int i = t * kNavKT + r;
+#pragma unroll
+          for (int cc = 0; cc < kCols; ++cc) {
+            const int c = tid + cc * kNavThreads;
+            wreg[r][cc] = (i < I && c < ncols) ? __ldg(wt + (size_t)i * O + ob + c) : 0.f;
+          }
+        }
+      };
+      auto stash = [&](int buf) {
+#pragma unroll
+        for (int r = 0; r < kNavKT; ++r)
+#pragma unroll
+          for (int cc = 0; cc < kCols; ++cc) wtile[(buf * kNavKT + r) * kNavOB + tid + cc * kNavThreads] = wreg[r][cc];
+      };
+      fetch(0);
+      stash(0);
+      __syncthreads();
       const float4* a4 = reinterpret_cast<const float4*>(cur + qg * 8);
-#pragma unroll 4
-      for (int i = 0; i < I; ++i) {
-        const float w0 = __ldg(wt + (size_t)i * O + o);
-        const float w1 = has1 ? __ldg(wt + (size_t)i * O + o1) : 0.f;
-        const float4 lo = a4[i * (kNavTQ / 4)];
-        const float4 hi = a4[i * (kNavTQ / 4) + 1];
-        acc0[0] = fmaf(lo.x, w0, acc0[0]); acc0[1] = fmaf(lo.y, w0, acc0[1]);
-        acc0[2] = fmaf(lo.z, w0, acc0[2]); acc0[3] = fmaf(lo.w, w0, acc0[3]);
-        acc0[4] = fmaf(hi.x, w0, acc0[4]); acc0[5] = fmaf(hi.y, w0, acc0[5]);
-        acc0[6] = fmaf(hi.z, w0, acc0[6]); acc0[7] = fmaf(hi.w, w0, acc0[7]);
-        acc1[0] = fmaf(lo.x, w1, acc1[0]); acc1[1] = fmaf(lo.y, w1, acc1[1]);
-        acc1[2] = fmaf(lo.z, w1, acc1[2]); acc1[3] = fmaf(lo.w, w1, acc1[3]);
-        acc1[4] = fmaf(hi.x, w1, acc1[4]); acc1[5] = fmaf(hi.y, w1, acc1[5]);
-        acc1[6] = fmaf(hi.z, w1, acc1[6]); acc1[7] = fmaf(hi.w, w1, acc1[7]);
+      for (int t = 0; t < n_tiles; ++t) {
+        if (t + 1 < n_tiles) fetch(t + 1);
+        const float* w = wtile + (size_t)(t & 1) * kNavKT * kNavOB + og;
+        const float4* a = a4 + (size_t)t * kNavKT * (kNavTQ / 4);
+        const int rows = min(kNavKT, I - t * kNavKT);
+        if (rows == kNavKT) {
+          switch (nu) {
+            case 1: nav_tile_fma<1, true>(acc, w, a, rows); break;
+            case 2: nav_tile_fma<2, true>(acc, w, a, rows); break;
+            case 3: nav_tile_fma<3, true>(acc, w, a, rows); break;
+            default: nav_tile_fma<4, true>(acc, w, a, rows); break;
+          }
+        } else {
+          switch (nu) {
+            case 1: nav_tile_fma<1, false>(acc, w, a, rows); break;
+            case 2: nav_tile_fma<2, false>(acc, w, a, rows); break;
+            case 3: nav_tile_fma<3, false>(acc, w, a, rows); break;
+            default: nav_tile_fma<4, false>(acc, w, a, rows); break;
+          }
+        }
+        if (t + 1 < n_tiles) stash((t + 1) & 1);      // the other buffer: last read two barriers ago
+        __syncthreads();
       }
-      float4* d0p = reinterpret_cast<float4*>(nxt + (size_t)o * kNavTQ + qg * 8);
-      if (relu) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { acc0[j] = fmaxf(acc0[j], 0.f); acc1[j] = fmaxf(acc1[j], 0.f); }
-      }
-      d0p[0] = make_float4(acc0[0], acc0[1], acc0[2], acc0[3]);
-      d0p[1] = make_float4(acc0[4], acc0[5], acc0[6], acc0[7]);
-      if (has1) {
-        float4* d1p = reinterpret_cast<float4*>(nxt + (size_t)o1 * kNavTQ + qg * 8);
-        d1p[0] = make_float4(acc1[0], acc1[1], acc1[2], acc1[3]);
-        d1p[1] = make_float4(acc1[4], acc1[5], acc1[6], acc1[7]);
+      for (int u = 0; u < 4; ++u) {
+        const int o = ob + og + 64 * u;
+        if (o < O) {
+          if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[u][j] = fmaxf(acc[u][j], 0.f);
+          }
+          float4* dp = reinterpret_cast<float4*>(nxt + (size_t)o * kNavTQ + qg * 8);
+          dp[0] = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+          dp[1] = make_float4(acc[u][4], acc[u][5], acc[u][6], acc[u][7]);
+        }
       }
     }
     __syncthreads();
-    float* t = cur; cur = nxt; nxt = t;
+    float* tmp = cur; cur = nxt; nxt = tmp;
   }
 
   // cur = logits [C][TQ].  softmax statistics + n_top rounds of warp arg-max per query.
@@ -101,17 +168,43 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
   for (int qi = 0; qi < kNavTQ / (kNavThreads / 32); ++qi) {
     const int q = warp * (kNavTQ / (kNavThreads / 32)) + qi;
     if (q >= nq_here) break;                       // warp-uniform
+    // a lane's logits (classes lane, lane+32, ...) are read once into registers when C <= 256: the
+    // [class][query] layout makes a warp's column read a 32-way bank conflict, so do it once, not per round
+    const bool in_regs = C <= 32 * kNavRegC;
+    float lv[kNavRegC];
+#pragma unroll
+    for (int u = 0; u < kNavRegC; ++u) {
+      const int c = lane + 32 * u;
+      lv[u] = (in_regs && c < C) ? cur[c * kNavTQ + q] : kNegInf * 2.f;
+    }
     float m = kNegInf;
-    for (int c = lane; c < C; c += 32) m = fmaxf(m, cur[c * kNavTQ + q]);
+    if (in_regs) {
+#pragma unroll
+      for (int u = 0; u < kNavRegC; ++u) if (lane + 32 * u < C) m = fmaxf(m, lv[u]);
+    } else {
+      for (int c = lane; c < C; c += 32) m = fmaxf(m, cur[c * kNavTQ + q]);
+    }
     m = warp_max(m);
     float s = 0.f;
-    for (int c = lane; c < C; c += 32) s += expf(cur[c * kNavTQ + q] - m);
+    if (in_regs) {
+#pragma unroll
+      for (int u = 0; u < kNavRegC; ++u) if (lane + 32 * u < C) s += expf(lv[u] - m);
+    } else {
+      for (int c = lane; c < C; c += 32) s += expf(cur[c * kNavTQ + q] - m);
+    }
     s = warp_sum(s);
     for (int t = 0; t < n_top; ++t) {
       float bv = kNegInf; int bc = 0x7fffffff;
-      for (int c = lane; c < C; c += 32) {
-        const float v = cur[c * kNavTQ + q];
-        if (v > bv) { bv = v; bc = c; }            // strided scan is ascending in c: lowest c wins ties
+      if (in_regs) {
+#pragma unroll
+        for (int u = 0; u < kNavRegC; ++u) {
+          if (lv[u] > bv) { bv = lv[u]; bc = lane + 32 * u; }          // ascending in c: lowest c wins ties
+        }
+      } else {
+        for (int c = lane; c < C; c += 32) {
+          const float v = cur[c * kNavTQ + q];
+          if (v > bv) { bv = v; bc = c; }            // strided scan is ascending in c: lowest c wins ties
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -124,14 +217,21 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
         out_classes[(q0 + q) * n_top + t] = bc;
         if (out_probs) out_probs[(q0 + q) * n_top + t] = expf(bv - m) / s;
       }
-      if ((bc & 31) == lane) cur[bc * kNavTQ + q] = kNegInf * 2.f;   // mark taken (-inf)
+      if ((bc & 31) == lane) {                                       // mark taken (-inf)
+        if (in_regs) {
+#pragma unroll
+          for (int u = 0; u < kNavRegC; ++u) if ((bc >> 5) == u) lv[u] = kNegInf * 2.f;
+        } else {
+          cur[bc * kNavTQ + q] = kNegInf * 2.f;
+        }
+      }
       __syncwarp();
     }
   }
 }
 
 inline size_t nav_smem_bytes(const NavLayers& L) {
-  return (size_t)2 * L.max_width * kNavTQ * sizeof(float);
+  return ((size_t)2 * L.max_width * kNavTQ + (size_t)2 * kNavKT * kNavOB) * sizeof(float);
 }
 
 }  // namespace lmi

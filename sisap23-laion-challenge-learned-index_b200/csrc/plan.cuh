@@ -160,39 +160,55 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
 // One CTA per bucket: ordered compaction of the (query, rank) pairs routed to it.
 //   slot_pair int32 [n_slots]: pair index e = q*nb + r of every slot (bucket-major, e ascending)
 //   pair_slot int32 [nq*nb]  : slot of every pair, -1 if its bucket is empty / out of range
-__global__ void __launch_bounds__(256)
+constexpr int kScatterThreads = 1024;
+constexpr int kScatterPer = 4;                 // consecutive pairs per thread and round
+__global__ void __launch_bounds__(kScatterThreads)
 plan_scatter_kernel(const int32_t* __restrict__ top_cls, int64_t n_pairs, int C,
                     const int32_t* __restrict__ qoff, const int64_t* __restrict__ bucket_ptr,
                     int32_t* __restrict__ slot_pair, int32_t* __restrict__ pair_slot) {
+  // Every CTA scans the whole class list (160 KB at 10k x 4, L2 resident) and keeps the pairs of its
+  // bucket in ascending pair order.  The scan is latency-bound, so a round covers 4096 pairs (4 per
+  // thread, the next round's loads issued before this round's block scan) -- 10 rounds at 10k x 4.
   const int b = blockIdx.x;
-  __shared__ int s_warp[8];
-  __shared__ int s_base;
+  __shared__ int s_warp[2][kScatterThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool live = (bucket_ptr[b + 1] - bucket_ptr[b]) > 0;
-  if (tid == 0) s_base = qoff[b];
-  __syncthreads();
-  for (int64_t e0 = 0; e0 < n_pairs; e0 += 256) {
-    const int64_t e = e0 + tid;
-    const int c = (e < n_pairs) ? top_cls[e] : -1;
-    const bool mine = (c == b);
-    const unsigned bal = __ballot_sync(0xffffffffu, mine);
-    if (lane == 0) s_warp[warp] = __popc(bal);
-    __syncthreads();
+  int base = qoff[b];
+  auto load4 = [&](int64_t e0, int (&c)[kScatterPer]) {
+#pragma unroll
+    for (int i = 0; i < kScatterPer; ++i) c[i] = (e0 + i < n_pairs) ? top_cls[e0 + i] : -1;
+  };
+  constexpr int64_t kRound = (int64_t)kScatterThreads * kScatterPer;
+  int cur[kScatterPer], nxt[kScatterPer];
+  load4((int64_t)tid * kScatterPer, cur);
+  int buf = 0;
+  for (int64_t r0 = 0; r0 < n_pairs; r0 += kRound, buf ^= 1) {
+    const int64_t e0 = r0 + (int64_t)tid * kScatterPer;
+    if (r0 + kRound < n_pairs) load4(e0 + kRound, nxt);
+    int mine = 0;
+#pragma unroll
+    for (int i = 0; i < kScatterPer; ++i) mine += (cur[i] == b) ? 1 : 0;
+    int incl = mine;                                                   // inclusive scan over the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    if (lane == 31) s_warp[buf][warp] = incl;
+    __syncthreads();                                                   // (double-buffered: one barrier per round)
     int before = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) { const int v = s_warp[w]; if (w < warp) before += v; total += v; }
+    for (int w = 0; w < kScatterThreads / 32; ++w) { const int v = s_warp[buf][w]; if (w < warp) before += v; total += v; }
     if (mine) {
-      if (live) {
-        const int slot = s_base + before + __popc(bal & ((1u << lane) - 1u));
-        slot_pair[slot] = (int)e;
-        pair_slot[e] = slot;
-      } else {
-        pair_slot[e] = -1;
+      int slot = base + before + incl - mine;
+#pragma unroll
+      for (int i = 0; i < kScatterPer; ++i) {
+        if (cur[i] == b) {
+          if (live) { slot_pair[slot] = (int)(e0 + i); pair_slot[e0 + i] = slot; ++slot; }
+          else pair_slot[e0 + i] = -1;
+        }
       }
     }
-    __syncthreads();
-    if (tid == 0 && live) s_base += total;
-    __syncthreads();
+    if (live) base += total;
+#pragma unroll
+    for (int i = 0; i < kScatterPer; ++i) cur[i] = nxt[i];
   }
 }
 
