@@ -19,7 +19,7 @@
 namespace lmi {
 
 constexpr int kFinWarps = 8;
-constexpr int kFinRegE = 8;           // entries per lane of the register-resident selection (<= 256 entries per query)
+constexpr int kFinRegE = 16;          // entries per lane of the register-resident selection (<= 512 entries per query)
 constexpr int kFinMaxVec = 128;       // uint4 per row, d <= 1024
 constexpr double kCertEps = 2e-5;       // bound used by the exactness certificate
 
@@ -294,14 +294,35 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   }
 }
 
-// Multi-GPU: k best of world*k gathered entries per query.  One warp per query.
+// Multi-GPU: k best of world*k gathered entries per query.  One warp per query: the entries are staged in
+// shared memory (up to kMergeSmemE per query) and every lane ranks its own entries against all of them
+// (broadcast reads); larger inputs (world * k > kMergeSmemE) rank straight from global memory.
+constexpr int kMergeSmemE = 128;
 __global__ void __launch_bounds__(kFinWarps * 32)
 merge_partials_kernel(const Partial* __restrict__ gathered, int world, int64_t nq, int k,
                       double* __restrict__ out_dists, uint32_t* __restrict__ out_ids) {
+  __shared__ Partial s_e[kFinWarps][kMergeSmemE];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t qi = (int64_t)blockIdx.x * kFinWarps + warp;
   if (qi >= nq) return;
   const int E = world * k;
+  if (E <= kMergeSmemE) {
+    for (int t = lane; t < E; t += 32) {
+      const int w = t / k;
+      s_e[warp][t] = gathered[((int64_t)w * nq + qi) * k + (t - w * k)];
+    }
+    __syncwarp();
+    for (int t = lane; t < E; t += 32) {
+      const Partial pt = s_e[warp][t];
+      int ord = 0;
+      for (int u = 0; u < E; ++u) {
+        const Partial pu = s_e[warp][u];
+        ord += key_less(pu.dist, pu.rank, pu.id, u, pt.dist, pt.rank, pt.id, t) ? 1 : 0;
+      }
+      if (ord < k) { out_dists[qi * k + ord] = pt.dist; out_ids[qi * k + ord] = pt.id; }
+    }
+    return;
+  }
   for (int t = lane; t < E; t += 32) {
     const Partial pt = gathered[((int64_t)(t / k) * nq + qi) * k + (t % k)];
     int ord = 0;
