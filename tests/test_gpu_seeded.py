@@ -202,3 +202,34 @@ def test_small_chunks_many_work_items(case, rescore):
     ref_d, ref_a = _search(_index(c, 1), c, 5, 10)
     d, a = _search(_index(c, rescore, chunk_objects=512), c, 5, 10)
     assert (a == ref_a).all() and (d == ref_d).all()
+
+
+def test_config0_300k_shape():
+    """BASELINE.json configs[0] at its real shape -- 300K objects, C = 122, `-bp 6` -> 7 leaf buckets
+    (search/search.py:37-38), k = 10 -- on a 1,000-query sample the oracle finishes in seconds: ids exact
+    up to documented ties, distances to 1e-3 relative (observed ~1e-15), every query certified."""
+    import torch
+    from lmi_b200.synth import SynthSpec, make_synthetic
+    from lmi_b200.trainer import train_index
+    from lmi_b200.index import GpuLearnedIndex
+    from oracle import lmi_oracle as O
+    C, nb, k = 122, int(6 / 100 * 122), 10
+    assert nb == 7
+    spec = SynthSpec(n=300_000, nq=1_000, n_blobs=2000, sigma=0.55)
+    t = make_synthetic(spec, "cuda")
+    _, w, b = train_index(t["data_nav"], C, "MLP-5", sample=200_000, epochs=3)
+    a = {kk: v.cpu().numpy() for kk, v in t.items()}
+    pc = O.predict(a["data_nav"], w, b)
+    _, classes = O.predict_proba(a["queries_nav"], w, b)
+    li = GpuLearnedIndex(C).set_model(w, b)
+    assert (li.model.predict(a["data_nav"]) != pc).mean() < 1e-4          # N1: argmax bucket of all 300K objects (fp32 near-ties aside)
+    li.prepare(a["data_f16"], pc)
+    d, ids = li.search(None, a["queries_nav"], a["data_f16"], a["queries_f16"], pc, n_buckets=nb, k=k)
+    _, cls = li.model.predict_proba(a["queries_nav"], n_top=nb)
+    ok = (np.sort(cls, 1) == np.sort(classes[:, :nb], 1)).all(1)
+    assert ok.mean() > 0.99
+    od, oa = O.search_intended(classes, a["data_f16"], a["queries_f16"], pc, nb, k)
+    assert_ids_equal_up_to_ties(ids[ok], d[ok], oa[ok], od[ok], what="config 0 (300K, 7 buckets)")
+    np.testing.assert_allclose(d[ok], od[ok], rtol=1e-3, atol=1e-9)
+    st = li.stats()
+    assert st["n_uncertified"] == 0 and st["rescore_kernel"] == "rescore_ts_kernel"
