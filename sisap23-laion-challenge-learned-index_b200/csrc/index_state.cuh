@@ -48,6 +48,8 @@ struct lmi_index {
   int num_sms = 148;
   int d_nav = 96, d = 768, C = 0;
   cudaStream_t stream = nullptr;            // stream of the host-buffer entry points
+  cudaStream_t copy_stream = nullptr;       // uploads the fp16 queries while K1/K2 run (lmi_search)
+  cudaEvent_t ev_q16 = nullptr;
 
   // options
   int rescore = LMI_RESCORE_TC;

@@ -79,6 +79,8 @@ int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories) 
   idx->num_sms = prop.multiProcessorCount;
   idx->d_nav = d_nav; idx->d = d; idx->C = n_categories;
   LMI_CUDA(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
+  LMI_CUDA(cudaStreamCreateWithFlags(&idx->copy_stream, cudaStreamNonBlocking));
+  LMI_CUDA(cudaEventCreateWithFlags(&idx->ev_q16, cudaEventDisableTiming));
   for (auto& e : idx->ev) LMI_CUDA(cudaEventCreate(&e));
   for (auto& pr : idx->ev_k3) for (auto& e : pr) LMI_CUDA(cudaEventCreate(&e));
   LMI_CUDA(cudaMallocHost(&idx->h_scalars, sizeof(PlanScalars)));
@@ -105,6 +107,8 @@ void lmi_destroy(lmi_index* idx) {
   for (auto& e : idx->ev) if (e) cudaEventDestroy(e);
   for (auto& pr : idx->ev_k3) for (auto& e : pr) if (e) cudaEventDestroy(e);
   if (idx->stream) cudaStreamDestroy(idx->stream);
+  if (idx->copy_stream) cudaStreamDestroy(idx->copy_stream);
+  if (idx->ev_q16) cudaEventDestroy(idx->ev_q16);
   delete idx;
 }
 

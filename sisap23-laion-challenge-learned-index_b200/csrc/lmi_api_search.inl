@@ -87,7 +87,7 @@ static int choose_chunk(const lmi_index* idx, int64_t nq, int nb, int KP) {
 // list: navigation (search) or caller-supplied categories (search_rank, nb = 1).
 static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls64_dev, const uint16_t* q16_dev,
                       int64_t nq, int nb, int k, const double* thr_dev, int mode, double* out_d, uint32_t* out_i,
-                      Partial* out_p, cudaStream_t st) {
+                      Partial* out_p, cudaStream_t st, cudaEvent_t q16_ready = nullptr) {
   if (!idx->has_store) return set_error(LMI_ERR_STATE, "bucket store not built (lmi_store_* / lmi_set_buckets)");
   if (q_nav_dev && !idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");   // LearnedIndex.py:60
   if (nq <= 0 || nq > (1 << 24)) return set_error(LMI_ERR_ARG, "nq out of range");
@@ -170,6 +170,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   plan_scatter_kernel<<<C, kScatterThreads, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
                                          idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
   plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());
+  // the fp16 queries are first read here (host-buffer entry point: they were uploaded on the copy stream
+  // while K1/K2 ran)
+  if (q16_ready) LMI_CUDA(cudaStreamWaitEvent(st, q16_ready, 0));
   if (use_tc)   // A operand of the tensor-core GEMM: query rows in bucket order
     gather_queries_kernel<<<idx->num_sms * 4, 256, 0, st>>>(q16_dev, idx->slot_pair.as<int32_t>(),
                                                             idx->scalars.as<PlanScalars>(), nb, d, idx->qg.as<uint16_t>());
@@ -256,10 +259,14 @@ int lmi_search(lmi_index* idx, const float* q_nav, const uint16_t* q_f16, int64_
   LMI_CUDA(idx->ws_q16.reserve((size_t)nq * idx->d * 2));
   LMI_CUDA(idx->ws_out_d.reserve((size_t)nq * k * 8));
   LMI_CUDA(idx->ws_out_i.reserve((size_t)nq * k * 4));
+  // navigation needs only the pca96 queries: the (4x larger) fp16 upload overlaps K1/K2 on a second stream.
+  // (ws_q16 is free: the previous call on this index synchronised its stream before returning)
   LMI_CUDA(cudaMemcpyAsync(idx->ws_qnav.p, q_nav, (size_t)nq * idx->d_nav * 4, cudaMemcpyHostToDevice, st));
-  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, q_f16, (size_t)nq * idx->d * 2, cudaMemcpyHostToDevice, st));
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, q_f16, (size_t)nq * idx->d * 2, cudaMemcpyHostToDevice, idx->copy_stream));
+  LMI_CUDA(cudaEventRecord(idx->ev_q16, idx->copy_stream));
   int rc = run_search(idx, idx->ws_qnav.as<float>(), nullptr, idx->ws_q16.as<uint16_t>(), nq, n_buckets, k, nullptr, 0,
-                      idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st);
+                      idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st, idx->ev_q16);
+  if (rc != LMI_OK) { cudaStreamSynchronize(idx->copy_stream); return rc; }
   if (rc != LMI_OK) return rc;
   LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
   LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
