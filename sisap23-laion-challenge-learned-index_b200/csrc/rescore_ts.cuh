@@ -208,6 +208,14 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
           }
         }
       }
+      // Producer tail: every stage must have been retired by BOTH CTAs before this CTA may exit.  The
+      // peer's tcgen05.commit arrives on this CTA's empty barriers asynchronously (when its MMAs finish),
+      // not ordered by the final cluster barrier; an arrive that lands in the shared memory of a CTA
+      // that has already exited is a fault (seen as a rare "unspecified launch failure" with short items).
+      for (int s = 0; s < STAGES; ++s) {
+        ptx::mbar_wait(ptx::smem_u32(&empty_bar[stage]), phase ^ 1);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
     }
   } else if (warp == 1 || warp == 6) {
     // ===================== MMA issuers (two warps) =====================
@@ -231,20 +239,16 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       ptx::mbar_wait(ptx::smem_u32(afull_bar), a_phase);             // this item's queries are in TMEM
       a_phase ^= 1;
       for (int t = 0; t < n_tiles; ++t, ++g) {
-        if ((int)(g & 1u) != parity) {             // the other warp's tile: step over its stages
-          if constexpr (STAGES >= 4) {
-            // ring longer than a tile: when this warp later waits on a stage, the stage's previous
-            // phase is complete by construction (its refill needed that phase consumed)
-            stage += k_stages;
-            if (stage >= STAGES) { stage -= STAGES; phase ^= 1; }
-          } else {
-            // short ring (k' = 128 leaves room for two stages): a stage comes round again inside one
-            // tile, and a parity wait for phase n+1 passes at once while the barrier is still in
-            // phase n -- so observe every phase of the skipped stages instead of counting them
-            for (int ks = 0; ks < k_stages; ++ks) {
-              ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
-              if (++stage == STAGES) { stage = 0; phase ^= 1; }
-            }
+        if ((int)(g & 1u) != parity) {
+          // The other warp's tile: OBSERVE every stage of it becoming full instead of just counting past
+          // them.  A parity wait for use n+1 of a stage returns at once while the barrier is still in
+          // use n, so a warp may only wait for a phase after it has seen the previous one complete.  With
+          // a ring shorter than two tiles a stage comes round again inside the other warp's tile (k' = 128
+          // always; longer rings only if TMA completions were reordered by three stages) -- observing the
+          // phases makes the scheme independent of both.  The stages are full long before this warp's own.
+          for (int ks = 0; ks < k_stages; ++ks) {
+            ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           continue;
         }
