@@ -233,3 +233,27 @@ def test_config0_300k_shape():
     np.testing.assert_allclose(d[ok], od[ok], rtol=1e-3, atol=1e-9)
     st = li.stats()
     assert st["n_uncertified"] == 0 and st["rescore_kernel"] == "rescore_ts_kernel"
+
+
+@pytest.mark.parametrize("nb,k", [(1, 10), (2, 100)])
+def test_short_items_repeated_launches(case, nb, k):
+    """Many back-to-back launches over short work items (one query tile per bucket -> plain pairs and
+    dummy entries, 256-object chunks): the kernel's cross-CTA barrier protocol must neither fault nor
+    change the answer.  (Round 1 had a rare fault here: an MMA warp waited for a stage phase it had not
+    seen the predecessor of, and CTAs could exit with the peer's commit arrives still in flight.)"""
+    import torch
+    from lmi_b200.index import GpuLearnedIndex
+    c = case
+    li = GpuLearnedIndex(c["C"], rank=3, world=8, chunk_objects=256).set_model(c["weights"], c["biases"])
+    li.prepare(c["data_f16"], c["pred_categories"])
+    qn = torch.from_numpy(c["queries_nav"]).cuda()
+    qs = torch.from_numpy(c["queries_f16"]).cuda()
+    nq = qs.shape[0]
+    first = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device="cuda")
+    li.search_partial_device(qn, qs, nb, k, first)
+    p = torch.empty_like(first)
+    for _ in range(300):
+        li.search_partial_device(qn, qs, nb, k, p)
+    torch.cuda.synchronize()
+    assert torch.equal(p, first)
+    assert li.stats()["n_uncertified"] == 0
