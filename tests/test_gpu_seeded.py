@@ -131,16 +131,16 @@ def test_edge_cases():
         assert set(as_[2, :6].tolist()) == {1, 2, 3, 4, 5, 6}
 
 
+@pytest.mark.parametrize("nb,k", [(4, 10), (2, 100)], ids=["k10", "k100"])
 @pytest.mark.parametrize("policy", [0, 1], ids=["buckets", "stripes"])
 @pytest.mark.parametrize("world", [2, 3, 8])
-def test_sharded_merge_equals_single(case, world, policy):
+def test_sharded_merge_equals_single(case, world, policy, nb, k):
     """Every rank holds a shard; per-rank partial results merged by the merge kernel must equal the
     one-GPU result bit for bit (ids and distances).  Ranks are emulated as `world` indexes on one
     device; the all-gather is a concatenation."""
     import torch
     from lmi_b200.index import GpuLearnedIndex
     c = case
-    nb, k = 4, 10
     ref_d, ref_a = _search(_index(c, 1), c, nb, k)
     nq = c["queries_f16"].shape[0]
     qn = torch.from_numpy(c["queries_nav"]).cuda()
