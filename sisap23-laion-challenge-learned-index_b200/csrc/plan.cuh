@@ -53,18 +53,21 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
   //   0: slots (m_b)   1: items (qtiles*chunks)   2: plists (m_b*chunks)
   for (int base = 0; base < C; base += 1024) {
     const int b = base + tid;
-    long long m = 0, nobj = 0, ch = 0, qt = 0;
+    long long m = 0, nobj = 0, ch = 0, qt = 0, csize = chunk;
     if (b < C) {
       nobj = bucket_ptr[b + 1] - bucket_ptr[b];
       m = (nobj > 0) ? m_b[b] : 0;                 // empty bucket: contributes nothing (LearnedIndex.py:147)
       ch = (nobj + chunk - 1) / chunk;
+      // equal-sized chunks (multiples of 64 objects) instead of `chunk`-sized ones plus a short tail:
+      // uniform work items, and no near-empty item that still pays for loading its query tile
+      if (ch > 0) csize = min((long long)chunk, ((nobj + ch - 1) / ch + 63) / 64 * 64);
       qt = (m + kTileQ - 1) / kTileQ;
       chunks_b[b] = (int)ch;
       tot_pairs += m * nobj;
       if (m > 0) tot_objs += nobj;
       if (ch > 0) {
-        const long long last = nobj - (ch - 1) * chunk;
-        tot_padded += qt * kTileQ * ((ch - 1) * ((chunk + 63) / 64 * 64) + (last + 63) / 64 * 64);
+        const long long last = nobj - (ch - 1) * csize;
+        tot_padded += qt * kTileQ * ((ch - 1) * csize + (last + 63) / 64 * 64);
       }
     }
     // work list entries come in PAIRS (entries 2i, 2i+1 = one item of a 2-CTA cluster of the
@@ -108,8 +111,8 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
           } else {
             wi.slot_base = (int)excl[0] + (int)t * kTileQ;
             wi.rows = (int)min((long long)kTileQ, m - t * kTileQ);
-            wi.obj_begin = (int)(obj0 + c * chunk);
-            wi.obj_count = (int)min((long long)chunk, nobj - c * chunk);
+            wi.obj_begin = (int)(obj0 + c * csize);
+            wi.obj_count = (int)min(csize, nobj - c * csize);
             wi.plist_base = excl[2] + t * kTileQ * ch + c;
             wi.plist_stride = (int)ch;
             wi.bucket = b;
