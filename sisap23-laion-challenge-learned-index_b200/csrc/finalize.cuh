@@ -19,7 +19,7 @@
 namespace lmi {
 
 constexpr int kFinWarps = 8;
-constexpr int kFinRegE = 16;          // entries per lane of the register-resident selection (<= 512 entries per query)
+constexpr int kFinRegE = 24;          // entries per lane of the register-resident selection (<= 768 entries per query)
 constexpr int kFinMaxVec = 128;       // uint4 per row, d <= 1024
 constexpr double kCertEps = 2e-5;       // bound used by the exactness certificate
 
@@ -96,28 +96,27 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   }
   if (fast) {
     const int total = s_rcum[warp][nb];
-    float es[kFinRegE]; int32_t ep[kFinRegE]; int er[kFinRegE];
+    float es[kFinRegE]; int32_t ep[kFinRegE];
 #pragma unroll
     for (int u = 0; u < kFinRegE; ++u) {
       const int g = lane + 32 * u;                 // entry number in (rank, list, position) order
-      es[u] = kNegInf * 2.f; ep[u] = -1; er[u] = 0;
+      es[u] = kNegInf * 2.f; ep[u] = -1;
       if (g < total) {
         int r = 0;
         while (g >= s_rcum[warp][r + 1]) ++r;
         const Cand c = plists[s_rbeg[warp][r] + (g - s_rcum[warp][r])];
-        if (c.pos >= 0) { es[u] = c.score; ep[u] = c.pos; er[u] = r; }
+        if (c.pos >= 0) { es[u] = c.score; ep[u] = c.pos; }
       }
     }
     for (int t = 0; t < R; ++t) {
       // per lane: best remaining entry with its payload (select chains only: the arrays stay in registers)
-      float best_s = kNegInf * 2.f; int best_g = 0x7fffffff; int32_t best_p = -1; int best_r = 0;
+      float best_s = kNegInf * 2.f; int best_g = 0x7fffffff; int32_t best_p = -1;
 #pragma unroll
       for (int u = 0; u < kFinRegE; ++u) {         // ascending g per lane: strict '>' keeps the lowest g of equal scores
         const bool better = ep[u] >= 0 && es[u] > best_s;
         best_s = better ? es[u] : best_s;
         best_g = better ? lane + 32 * u : best_g;
         best_p = better ? ep[u] : best_p;
-        best_r = better ? er[u] : best_r;
       }
       float win_s = best_s; int win_g = best_g;
 #pragma unroll
@@ -128,7 +127,9 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
       }
       if (win_g == 0x7fffffff) break;              // no more valid entries (warp-uniform)
       if (win_g == best_g) {                       // exactly one lane
-        s_pos[warp][t] = best_p; s_rank[warp][t] = (uint32_t)best_r; s_dist[warp][t] = (double)best_s;
+        int r = 0;                                 // bucket rank of the entry: the range it falls in
+        while (win_g >= s_rcum[warp][r + 1]) ++r;
+        s_pos[warp][t] = best_p; s_rank[warp][t] = (uint32_t)r; s_dist[warp][t] = (double)best_s;
       }
 #pragma unroll
       for (int u = 0; u < kFinRegE; ++u) ep[u] = (lane + 32 * u == win_g) ? -1 : ep[u];     // taken
