@@ -480,14 +480,10 @@ def run_b200(args):
                 check(li._lib.lmi_search(li._h, C.c_void_p(h_qn.ctypes.data), C.c_void_p(h_qs.ctypes.data), nq, nb, k,
                                          C.c_void_p(e_d.ctypes.data), C.c_void_p(e_i.ctypes.data)))
         else:
-            d_qn, d_qs = torch.empty_like(qn), torch.empty_like(qs)
-            d_out = (torch.empty_like(out[0]), torch.empty_like(out[1]))
-
+            # the public multi-GPU call: every rank uploads its slice of the queries, NVLink all-gather,
+            # sharded search, merged result back to the host
             def e2e_step():
-                d_qn.copy_(h_qn_t, non_blocking=True); d_qs.copy_(h_qs_t, non_blocking=True)
-                ds.search_device(d_qn, d_qs, nb, k, d_out)
-                e_d_t.copy_(d_out[0], non_blocking=True); e_i_t.copy_(d_out[1], non_blocking=True)
-                torch.cuda.current_stream().synchronize()
+                ds.search_host(h_qn_t, h_qs_t, nb, k, (e_d_t, e_i_t))
         for _ in range(3):
             e2e_step()
         barrier()
@@ -501,9 +497,13 @@ def run_b200(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             e2e_s = float(tt.item())
         assert (e_i_t.numpy() == out[1].cpu().numpy()).all(), "e2e result differs from the device-resident result"
-        e2e = dict(value=nq / e2e_s, unit="queries/s", h2d_bytes_per_step=int(h_qn_t.numel() * 4 + h_qs_t.numel() * 2),
-                   d2h_bytes_per_step=int(e_d_t.numel() * 8 + e_i_t.numel() * 4), ms_per_step=e2e_s * 1e3,
-                   per_rank="every rank copies the replicated queries in and the merged result out" if world > 1 else None)
+        per_rank_rows = (nq + world - 1) // world
+        e2e = dict(value=nq / e2e_s, unit="queries/s",
+                   h2d_bytes_per_step=int(h_qn_t.numel() * 4 + h_qs_t.numel() * 2) if world == 1 else
+                   int(per_rank_rows * (h_qn_t.shape[1] * 4 + h_qs_t.shape[1] * 2)) * world,
+                   d2h_bytes_per_step=int(e_d_t.numel() * 8 + e_i_t.numel() * 4) * (world if world > 1 else 1), ms_per_step=e2e_s * 1e3,
+                   per_rank=("every rank uploads 1/N of the queries (all-gathered over NVLink) and reads the merged result back; "
+                             "bytes are summed over ranks") if world > 1 else None)
 
     # ---- quality: recall@10 against an independent brute force; certificate ----
     recall = None

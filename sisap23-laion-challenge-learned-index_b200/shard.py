@@ -121,3 +121,39 @@ class DistributedSearch:
         self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
         self.dist.all_gather_into_tensor(gathered, part, group=self.group)      # the one exchange step
         return self.li.merge_partials_device(gathered, self.world, nq, k, out)
+
+    def search_host(self, q_nav_host, q_f16_host, n_buckets, k, out_host=None):
+        """End-to-end step from (pinned) host tensors that every rank holds: each rank uploads only ITS slice
+        of the queries over PCIe and the ranks all-gather the slices over NVLink (19.2 MB at 10k queries: tens
+        of microseconds instead of a full upload per rank), then the sharded search, then the merged result is
+        copied back to the host.  Returns (dists f64 [nq,k], ids i32 [nq,k]) as pinned host tensors."""
+        import torch
+        nq = int(q_f16_host.shape[0])
+        dev = torch.device("cuda", self.li.device)
+        W, r = self.world, (self.dist.get_rank(self.group) if self.world > 1 else 0)
+        per = (nq + W - 1) // W                                  # rows per rank (last slice zero-padded)
+        key = (nq, int(q_nav_host.shape[1]), int(q_f16_host.shape[1]), k)
+        if getattr(self, "_hbuf_key", None) != key:
+            self._hbuf_key = key
+            self._qn_all = torch.empty(W * per, q_nav_host.shape[1], dtype=torch.float32, device=dev)
+            self._qs_all = torch.empty(W * per, q_f16_host.shape[1], dtype=torch.float16, device=dev)
+            self._qn_mine = torch.zeros(per, q_nav_host.shape[1], dtype=torch.float32, device=dev)
+            self._qs_mine = torch.zeros(per, q_f16_host.shape[1], dtype=torch.float16, device=dev)
+            self._out_dev = (torch.empty(nq, k, dtype=torch.float64, device=dev), torch.empty(nq, k, dtype=torch.int32, device=dev))
+            self._out_host = (torch.empty(nq, k, dtype=torch.float64).pin_memory(), torch.empty(nq, k, dtype=torch.int32).pin_memory())
+        lo, hi = min(nq, r * per), min(nq, (r + 1) * per)
+        if W == 1:
+            qn_all, qs_all = self._qn_all[:nq], self._qs_all[:nq]
+            qn_all.copy_(q_nav_host, non_blocking=True); qs_all.copy_(q_f16_host, non_blocking=True)
+        else:
+            if hi > lo:
+                self._qn_mine[:hi - lo].copy_(q_nav_host[lo:hi], non_blocking=True)
+                self._qs_mine[:hi - lo].copy_(q_f16_host[lo:hi], non_blocking=True)
+            self.dist.all_gather_into_tensor(self._qn_all, self._qn_mine, group=self.group)
+            self.dist.all_gather_into_tensor(self._qs_all, self._qs_mine, group=self.group)
+            qn_all, qs_all = self._qn_all[:nq], self._qs_all[:nq]
+        self.search_device(qn_all, qs_all, n_buckets, k, self._out_dev)
+        oh = out_host if out_host is not None else self._out_host
+        oh[0].copy_(self._out_dev[0], non_blocking=True); oh[1].copy_(self._out_dev[1], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return oh
