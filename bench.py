@@ -45,7 +45,7 @@ def parse_args():
     p.add_argument("--model-type", default="MLP-5")
     p.add_argument("--blobs", type=int, default=2000)
     p.add_argument("--sigma", type=float, default=0.55)
-    p.add_argument("--rescore", default="tc", choices=["tc", "tc_ss", "simt"])
+    p.add_argument("--rescore", default="tc", choices=["tc", "tc_ss", "simt", "tc_pair"])
     p.add_argument("--chunk-objects", type=int, default=None)
     p.add_argument("--shard", default="buckets", choices=["buckets", "stripes"])
     p.add_argument("--presharded", action="store_true",
@@ -362,7 +362,7 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
-    from lmi_b200.index import GpuLearnedIndex, RESCORE_TC, RESCORE_TC_SS, RESCORE_SIMT, SHARD_BUCKETS, SHARD_STRIPES
+    from lmi_b200.index import GpuLearnedIndex, RESCORE_TC, RESCORE_TC_SS, RESCORE_SIMT, RESCORE_TC_PAIR, SHARD_BUCKETS, SHARD_STRIPES
     peaks = load_peaks()
     presharded = args.presharded or args.n > 30_000_000
     if presharded and args.n * 768 * 2 * 2.1 / world > 170e9:
@@ -373,7 +373,7 @@ def run_b200(args):
 
     # presharded: an ordinary (unsharded) index over this rank's rows; the exchange + merge are the same
     li = GpuLearnedIndex(args.categories, device=local_rank,
-                         rescore={"tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT}[args.rescore],
+                         rescore={"tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT, "tc_pair": RESCORE_TC_PAIR}[args.rescore],
                          chunk_objects=args.chunk_objects, rank=0 if presharded else rank, world=1 if presharded else world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)
     li.set_model(inp["weights"], inp["biases"])

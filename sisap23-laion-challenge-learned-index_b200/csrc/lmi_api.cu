@@ -6,6 +6,7 @@
 #include "rescore_simt.cuh"
 #include "rescore_tc.cuh"
 #include "rescore_ts.cuh"
+#include "rescore_ts2.cuh"
 #include "finalize.cuh"
 
 namespace lmi {
@@ -116,8 +117,8 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   if (!idx || !name) return set_error(LMI_ERR_ARG, "NULL argument");
   std::string n(name);
   if (n == "rescore") {
-    if (value != LMI_RESCORE_SIMT && value != LMI_RESCORE_TC && value != LMI_RESCORE_TC_SS)
-      return set_error(LMI_ERR_ARG, "rescore: 0 (simt), 1 (tcgen05, queries in TMEM) or 2 (tcgen05, smem operands)");
+    if (value != LMI_RESCORE_SIMT && value != LMI_RESCORE_TC && value != LMI_RESCORE_TC_SS && value != LMI_RESCORE_TC_PAIR)
+      return set_error(LMI_ERR_ARG, "rescore: 0 (simt), 1 (tcgen05, queries in TMEM), 2 (tcgen05, smem operands) or 3 (tcgen05 CTA pairs)");
     idx->rescore = (int)value;
   } else if (n == "chunk_objects") {
     if (value != 0 && (value < 256 || value > (1 << 24))) return set_error(LMI_ERR_ARG, "chunk_objects out of range (0 = automatic)");

@@ -33,6 +33,25 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       idx->rescore_name = "rescore_ts_kernel";
     }
   }
+  if constexpr (KP <= 128) {
+    if (idx->kernel_now == LMI_RESCORE_TC_PAIR) {
+      done = true;
+      // 16 KB stages per CTA (half tiles) beside the [k' + 16][128] x 8 B candidate lists
+      constexpr int STAGES = (KP <= 32) ? 10 : (KP <= 64) ? 8 : 4;
+      auto kern = rescore_ts2_kernel<KP, STAGES>;
+      constexpr size_t smem = ts2_smem_bytes<KP, STAGES>();
+      static_assert(smem <= 227 * 1024, "rescore_ts2: shared memory budget");
+      static bool attr_done = false;
+      if (!attr_done) {
+        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+      }
+      kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+                                                        idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
+                                                        idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
+      idx->rescore_name = "rescore_ts2_kernel";
+    }
+  }
   if constexpr (KP <= 64) {
     if (idx->kernel_now == LMI_RESCORE_TC_SS) {
       done = true;
@@ -120,8 +139,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
     if (c < nb) top_nb_chunks += ch;
   }
   // entries: at most qtiles_b * chunks_b + 1 (dummy) per bucket
-  const int64_t items_a = qtiles_max * total_chunks + C;
-  const int64_t items_b = (n_pairs / kTileQ + C) * std::max<int64_t>(max_chunks, 1) + C;
+  // (pair mode of the CTA-pair kernel: an odd last tile becomes two entries -> one more per bucket and chunk)
+  const int64_t items_a = (qtiles_max + 1) * total_chunks + C;
+  const int64_t items_b = (n_pairs / kTileQ + 2 * C) * std::max<int64_t>(max_chunks, 1) + C;
   const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
   if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
@@ -131,11 +151,12 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   int kernel = LMI_RESCORE_SIMT;
   if (idx->rescore != LMI_RESCORE_SIMT && idx->tmap_x_ok) {
     if (idx->rescore == LMI_RESCORE_TC && d <= 2 * kTsACols) kernel = LMI_RESCORE_TC;        // k' <= 128
+    else if (idx->rescore == LMI_RESCORE_TC_PAIR && d <= 2 * kTsACols) kernel = LMI_RESCORE_TC_PAIR;
     else if (KP <= 64) kernel = LMI_RESCORE_TC_SS;
   }
   idx->kernel_now = kernel;
   const bool use_tc = (kernel == LMI_RESCORE_TC_SS);       // SS kernel: needs the bucket-ordered query copy
-  if (kernel == LMI_RESCORE_TC) {
+  if (kernel == LMI_RESCORE_TC || kernel == LMI_RESCORE_TC_PAIR) {
     LMI_CUDA(idx->qthr.reserve((size_t)nq * 4));
     LMI_CUDA(cudaMemsetAsync(idx->qthr.p, 0, (size_t)nq * 4, st));
   }
@@ -166,7 +187,8 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   plan_count_kernel<<<idx->num_sms * 2, 256, 0, st>>>(top, n_pairs, C, idx->m_b.as<int32_t>());
   plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, chunk,
                                         idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
-                                        idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>());
+                                        idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>(),
+                                        kernel == LMI_RESCORE_TC_PAIR ? 1 : 0);
   plan_scatter_kernel<<<C, kScatterThreads, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
                                          idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
   plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());

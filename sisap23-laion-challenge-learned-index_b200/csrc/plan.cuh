@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(1024)
 plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ bucket_ptr, int C,
                   int chunk, int32_t* __restrict__ qoff, int32_t* __restrict__ chunks_b,
                   int64_t* __restrict__ plist_base, WorkItem* __restrict__ items, int max_items,
-                  PlanScalars* __restrict__ sc) {
+                  PlanScalars* __restrict__ sc, int pair_mode = 0) {
   __shared__ long long s_scan[1024];
   __shared__ long long s_carry[3];
   const int tid = threadIdx.x;
@@ -67,7 +67,8 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       if (m > 0) tot_objs += nobj;
       if (ch > 0) {
         const long long last = nobj - (ch - 1) * csize;
-        tot_padded += qt * kTileQ * ((ch - 1) * csize + (last + 63) / 64 * 64);
+        const long long qt_mma = pair_mode ? (qt + 1) / 2 * 2 : qt;      // pair mode: an odd last tile costs a full pair
+        tot_padded += qt_mma * kTileQ * ((ch - 1) * csize + (last + 63) / 64 * 64);
       }
     }
     // work list entries come in PAIRS (entries 2i, 2i+1 = one item of a 2-CTA cluster of the
@@ -75,8 +76,10 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
     //   shared pair : query tiles 2p and 2p+1 of the same object chunk  (flag kItemShared: the
     //                 cluster loads the chunk once and multicasts it to both CTAs)
     //   plain pair  : the odd last query tile of chunks c and c+1 (or a dummy entry)
-    const long long pairs_per_chunk = qt / 2;
-    const long long n_pair = ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
+    // pair mode (rescore_ts2.cuh, CTA-pair MMAs: a cluster can only run shared pairs): ceil(qt / 2) shared
+    //   pairs per chunk; an odd last query tile is split into two half tiles of the same chunk
+    const long long pairs_per_chunk = pair_mode ? (qt + 1) / 2 : qt / 2;
+    const long long n_pair = pair_mode ? ch * pairs_per_chunk : ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
     long long vals[3] = {m, 2 * n_pair, m * ch};
     long long excl[3];
     for (int w = 0; w < 3; ++w) {
@@ -122,6 +125,37 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
         }
         ++it;
       };
+      // one entry with an explicit row range [row0, row0 + rows) of the bucket's query list
+      auto emit_rows = [&](long long c, long long row0, long long rows) {
+        if (it < max_items) {
+          WorkItem wi;
+          wi.slot_base = (int)excl[0] + (int)row0;
+          wi.rows = (int)rows;
+          wi.obj_begin = (int)(obj0 + c * csize);
+          wi.obj_count = (int)min(csize, nobj - c * csize);
+          wi.plist_base = excl[2] + row0 * ch + c;
+          wi.plist_stride = (int)ch;
+          wi.bucket = b;
+          wi.flags = kItemShared;
+          wi.pad = 0;
+          items[it] = wi;
+        }
+        ++it;
+      };
+      if (pair_mode) {
+        for (long long c = 0; c < ch; ++c)
+          for (long long p = 0; p < pairs_per_chunk; ++p) {
+            const long long r0 = 2 * p * kTileQ;
+            if (2 * p + 1 < qt) {
+              emit_rows(c, r0, kTileQ);
+              emit_rows(c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ));
+            } else {                                           // odd last tile: two halves (the second may be empty)
+              const long long r = m - r0, h = (r + 1) / 2;
+              emit_rows(c, r0, h);
+              emit_rows(c, r0 + h, r - h);
+            }
+          }
+      } else
       for (long long c0 = 0; c0 < ch; c0 += 2) {
         for (long long c = c0; c < min(ch, c0 + 2); ++c)
           for (long long p = 0; p < pairs_per_chunk; ++p) { emit(c, 2 * p, kItemShared); emit(c, 2 * p + 1, kItemShared); }

@@ -24,7 +24,7 @@ import numpy as np
 from . import _lib
 from ._lib import LmiStats, check
 
-RESCORE_SIMT, RESCORE_TC, RESCORE_TC_SS = 0, 1, 2
+RESCORE_SIMT, RESCORE_TC, RESCORE_TC_SS, RESCORE_TC_PAIR = 0, 1, 2, 3
 SHARD_BUCKETS, SHARD_STRIPES = 0, 1
 
 

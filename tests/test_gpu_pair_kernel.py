@@ -1,0 +1,101 @@
+"""GPU parity of the CTA-pair rescoring kernel (option rescore = 3, ``rescore_ts2_kernel``: tcgen05
+``cta_group::2`` MMAs, planner pair mode) against the default kernel, the oracle and the reference's
+golden vectors.  Every rescoring kernel hands the same survivors to the same float64 refine, so the
+final (dists, ids) must be BIT-IDENTICAL to the default kernel's.
+
+The kernel is experimental this round ("K3-pair"): these tests run only when
+``LMI_TEST_PAIR=1`` is set, so that the default ``-m gpu`` run covers exactly the shipped path.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import load_golden, GOLDEN_TAGS, rows_with_small_buckets, assert_ids_equal_up_to_ties
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("LMI_TEST_PAIR", "0") != "1",
+                                 reason="experimental CTA-pair kernel: set LMI_TEST_PAIR=1")]
+
+PAIR = 3
+
+
+def _golden_index(g, rescore, **kw):
+    from lmi_b200.index import GpuLearnedIndex
+    li = GpuLearnedIndex(g["n_categories"], d_nav=g["queries_nav"].shape[1], d=g["data_f16"].shape[1],
+                         rescore=rescore, **kw)
+    li.set_model(g["weights"], g["biases"])
+    return li
+
+
+@pytest.mark.parametrize("tag", GOLDEN_TAGS)
+def test_pair_kernel_matches_reference_and_oracle(tag):
+    from oracle import lmi_oracle as O
+    g = load_golden(tag)
+    li = _golden_index(g, PAIR)
+    for nb in g["bucket_list"]:
+        d, a = li.search(None, g["queries_nav"], g["data_f16"], g["queries_f16"], g["pred_categories"],
+                         n_buckets=nb, k=g["k"])
+        st = li.stats()
+        assert st["rescore_kernel"] == "rescore_ts2_kernel", st
+        ok = ~rows_with_small_buckets(g, nb)
+        assert_ids_equal_up_to_ties(a[ok], d[ok], g[f"clean_ids_nb{nb}"][ok], g[f"clean_dists_nb{nb}"][ok],
+                                    what=f"{tag} nb={nb} pair kernel vs reference")
+        od, oa = O.search_intended(g["classes"], g["data_f16"], g["queries_f16"], g["pred_categories"], nb, g["k"])
+        assert_ids_equal_up_to_ties(a, d, oa, od, what=f"{tag} nb={nb} pair kernel vs oracle")
+        np.testing.assert_allclose(d, od, rtol=1e-3, atol=1e-9)
+        assert st["n_uncertified"] == 0 and st["max_abs_score_err"] < 5e-6, st
+
+
+@pytest.fixture(scope="module")
+def case():
+    """40k x 768 LAION-shaped objects, 48 categories, MLP-5 (same recipe as test_gpu_seeded.case)."""
+    from lmi_b200.synth import SynthSpec, make_synthetic
+    from lmi_b200.trainer import train_index
+    from oracle import lmi_oracle as O
+    spec = SynthSpec(n=40_000, nq=600, n_blobs=400, sigma=0.6, pca_rows=20_000)
+    t = make_synthetic(spec, "cuda")
+    _, w, b = train_index(t["data_nav"], 48, "MLP-5", sample=40_000, epochs=4)
+    a = {k: v.cpu().numpy() for k, v in t.items()}
+    pc = O.predict(a["data_nav"], w, b)
+    _, classes = O.predict_proba(a["queries_nav"], w, b)
+    return dict(a, weights=w, biases=b, pred_categories=pc, classes=classes, C=48)
+
+
+def _index(c, rescore, **kw):
+    from lmi_b200.index import GpuLearnedIndex
+    li = GpuLearnedIndex(c["C"], rescore=rescore, **kw)
+    li.set_model(c["weights"], c["biases"])
+    li.prepare(c["data_f16"], c["pred_categories"])
+    return li
+
+
+def _search(li, c, nb, k):
+    return li.search(None, c["queries_nav"], c["data_f16"], c["queries_f16"], c["pred_categories"], n_buckets=nb, k=k)
+
+
+@pytest.mark.parametrize("nb,k,chunk", [(1, 10, 0), (4, 10, 0), (7, 10, 0), (4, 10, 512), (48, 10, 256),
+                                        (3, 50, 0), (2, 100, 0), (2, 100, 1024)])
+def test_pair_kernel_equals_default_kernel(case, nb, k, chunk):
+    c = case
+    li3 = _index(c, PAIR, chunk_objects=chunk)
+    d3, a3 = _search(li3, c, nb, k)
+    st = li3.stats()
+    assert st["rescore_kernel"] == "rescore_ts2_kernel" and st["n_uncertified"] == 0, st
+    assert st["n_work_items"] % 2 == 0
+    d1, a1 = _search(_index(c, 1, chunk_objects=chunk), c, nb, k)
+    assert (a3 == a1).all()
+    assert (d3 == d1).all()
+    # repeated launches: deterministic, and the persistent state (barriers, tensor memory) is released cleanly
+    for _ in range(3):
+        d_, a_ = _search(li3, c, nb, k)
+        assert (a_ == a3).all() and (d_ == d3).all()
+
+
+def test_pair_kernel_search_single(case):
+    c = case
+    li3, li1 = _index(c, PAIR), _index(c, 1)
+    cat = c["classes"][:, 0]
+    d3, a3 = li3.search_single(None, c["data_f16"], c["queries_f16"], cat, k=10)
+    d1, a1 = li1.search_single(None, c["data_f16"], c["queries_f16"], cat, k=10)
+    assert (a3 == a1).all() and (d3 == d1).all()
