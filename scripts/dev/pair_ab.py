@@ -65,16 +65,20 @@ def main():
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "pair_ab.json"))
     ap.add_argument("--diag-only", action="store_true")
     ap.add_argument("--chunks", default="0,16128,64000", help="chunk_objects values tried for the pair kernel (0 = automatic)")
+    ap.add_argument("--dbg", default="", help="comma list of dbg_flags run for BOTH kernels after the A/B (results invalid by construction)")
+    ap.add_argument("--skip-diag", action="store_true")
     a = ap.parse_args()
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
-    report = {"diag": diag(256)}
-    print(json.dumps(report["diag"]), flush=True)
-    json.dump(report, open(a.out, "w"), indent=1)
-    report["diag_odd_tile"] = diag(300)          # 3 query tiles: a full pair + a split odd tile
-    print(json.dumps(report["diag_odd_tile"]), flush=True)
-    json.dump(report, open(a.out, "w"), indent=1)
-    if a.diag_only or report["diag"]["rows_mismatch"] or report["diag_odd_tile"]["rows_mismatch"]:
-        return
+    report = {}
+    if not a.skip_diag:
+        report["diag"] = diag(256)
+        print(json.dumps(report["diag"]), flush=True)
+        json.dump(report, open(a.out, "w"), indent=1)
+        report["diag_odd_tile"] = diag(300)          # 3 query tiles: a full pair + a split odd tile
+        print(json.dumps(report["diag_odd_tile"]), flush=True)
+        json.dump(report, open(a.out, "w"), indent=1)
+        if a.diag_only or report["diag"]["rows_mismatch"] or report["diag_odd_tile"]["rows_mismatch"]:
+            return
     import torch
     import bench
     sys.argv = [sys.argv[0], "--rows", str(a.rows)]
@@ -89,10 +93,13 @@ def main():
     nq, k, nb = args.nq, args.k, args.buckets
     runs = []
     ref = None
-    configs = [(1, 0)] + [(3, int(c)) for c in a.chunks.split(",")] + [(1, 0)]
-    for rescore, chunk in configs:
+    configs = [(1, 0, 0)] + [(3, int(c), 0) for c in a.chunks.split(",") if c != ""] + [(1, 0, 0)]
+    for f in [int(v) for v in a.dbg.split(",") if v != ""]:
+        configs += [(1, 0, f), (3, 0, f)]
+    for rescore, chunk, flags in configs:
         li.set_option("rescore", rescore)
         li.set_option("chunk_objects", chunk)
+        li.set_option("dbg_flags", flags)
         out = (torch.empty(nq, k, dtype=torch.float64, device=device), torch.empty(nq, k, dtype=torch.int32, device=device))
         for _ in range(3):
             li.search_device(qn, qs, nb, k, out)
@@ -109,7 +116,7 @@ def main():
         dd = out[0].cpu().numpy()
         if ref is None:
             ref = (dd, ids)
-        runs.append(dict(rescore=rescore, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
+        runs.append(dict(rescore=rescore, dbg_flags=flags, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
                          ms_per_search=ev0.elapsed_time(ev1) / a.steps, k3_ms_avg=st["ms_rescore_avg"],
                          k3_sm_mhz=st["k3_sm_mhz"], work_items=st["n_work_items"], pairs=st["pairs"],
                          padded_pairs=st["padded_pairs"], tile_efficiency=st["pairs"] / max(st["padded_pairs"], 1),
