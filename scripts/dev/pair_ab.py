@@ -67,6 +67,9 @@ def main():
     ap.add_argument("--chunks", default="0,16128,64000", help="chunk_objects values tried for the pair kernel (0 = automatic)")
     ap.add_argument("--dbg", default="", help="comma list of dbg_flags run for BOTH kernels after the A/B (results invalid by construction)")
     ap.add_argument("--skip-diag", action="store_true")
+    ap.add_argument("--seq", default="", help="explicit run sequence 'rescore:chunk:flags,...' (replaces the default A/B order; "
+                                              "interleave variants -- the power-capped clock drifts over a process lifetime)")
+    ap.add_argument("--dbg-pair-only", action="store_true", help="run the --dbg flags on the pair kernel only")
     a = ap.parse_args()
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     report = {}
@@ -95,7 +98,9 @@ def main():
     ref = None
     configs = [(1, 0, 0)] + [(3, int(c), 0) for c in a.chunks.split(",") if c != ""] + [(1, 0, 0)]
     for f in [int(v) for v in a.dbg.split(",") if v != ""]:
-        configs += [(1, 0, f), (3, 0, f)]
+        configs += [(3, 0, f)] if a.dbg_pair_only else [(1, 0, f), (3, 0, f)]
+    if a.seq:
+        configs = [tuple(int(v) for v in item.split(":")) for item in a.seq.split(",")]
     for rescore, chunk, flags in configs:
         li.set_option("rescore", rescore)
         li.set_option("chunk_objects", chunk)

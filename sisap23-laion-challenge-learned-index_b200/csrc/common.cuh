@@ -26,6 +26,7 @@ struct __align__(16) WorkItem {
   int32_t pad;
 };
 constexpr int kItemShared = 1;
+constexpr int kItemHalf = 2;      // CTA-pair kernel: half tile (<= 64 rows per CTA), scored with M = 128 pair MMAs
 
 struct __align__(8) Cand {  // entry of a partial top-k' list
   float score;              // dot(q, x) * inv_norm(x)  (cosine times |q|)

@@ -38,17 +38,16 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       done = true;
       // 16 KB stages per CTA (half tiles) beside the [k' + 16][128] x 8 B candidate lists
       constexpr int STAGES = (KP <= 32) ? 10 : (KP <= 64) ? 8 : 4;
-      auto kern = rescore_ts2_kernel<KP, STAGES>;
-      constexpr size_t smem = ts2_smem_bytes<KP, STAGES>();
-      static_assert(smem <= 227 * 1024, "rescore_ts2: shared memory budget");
-      static bool attr_done = false;
-      if (!attr_done) {
-        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-      }
-      kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
-                                                        idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                        idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
+      auto launch = [&](auto kern, size_t smem) -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+                                                          idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
+                                                          idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
+        return cudaSuccess;
+      };
+      static_assert(ts2_smem_bytes<KP, STAGES>() <= 227 * 1024, "rescore_ts2: shared memory budget");
+      LMI_CUDA(launch(rescore_ts2_kernel<KP, STAGES>, ts2_smem_bytes<KP, STAGES>()));
       idx->rescore_name = "rescore_ts2_kernel";
     }
   }

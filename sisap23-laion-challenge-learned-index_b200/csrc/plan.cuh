@@ -67,8 +67,8 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       if (m > 0) tot_objs += nobj;
       if (ch > 0) {
         const long long last = nobj - (ch - 1) * csize;
-        const long long qt_mma = pair_mode ? (qt + 1) / 2 * 2 : qt;      // pair mode: an odd last tile costs a full pair
-        tot_padded += qt_mma * kTileQ * ((ch - 1) * csize + (last + 63) / 64 * 64);
+        // (pair mode: an odd last tile runs as a half-tile pair with M = 128 MMAs = the tensor time of one tile)
+        tot_padded += qt * kTileQ * ((ch - 1) * csize + (last + 63) / 64 * 64);
       }
     }
     // work list entries come in PAIRS (entries 2i, 2i+1 = one item of a 2-CTA cluster of the
@@ -77,7 +77,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
     //                 cluster loads the chunk once and multicasts it to both CTAs)
     //   plain pair  : the odd last query tile of chunks c and c+1 (or a dummy entry)
     // pair mode (rescore_ts2.cuh, CTA-pair MMAs: a cluster can only run shared pairs): ceil(qt / 2) shared
-    //   pairs per chunk; an odd last query tile is split into two half tiles of the same chunk
+    //   pairs per chunk; an odd last query tile is split into two half tiles (<= 64 rows each, kItemHalf) of the same chunk
     const long long pairs_per_chunk = pair_mode ? (qt + 1) / 2 : qt / 2;
     const long long n_pair = pair_mode ? ch * pairs_per_chunk : ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
     long long vals[3] = {m, 2 * n_pair, m * ch};
@@ -126,7 +126,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
         ++it;
       };
       // one entry with an explicit row range [row0, row0 + rows) of the bucket's query list
-      auto emit_rows = [&](long long c, long long row0, long long rows) {
+      auto emit_rows = [&](long long c, long long row0, long long rows, int flags) {
         if (it < max_items) {
           WorkItem wi;
           wi.slot_base = (int)excl[0] + (int)row0;
@@ -136,7 +136,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
           wi.plist_base = excl[2] + row0 * ch + c;
           wi.plist_stride = (int)ch;
           wi.bucket = b;
-          wi.flags = kItemShared;
+          wi.flags = flags;
           wi.pad = 0;
           items[it] = wi;
         }
@@ -147,12 +147,12 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
           for (long long p = 0; p < pairs_per_chunk; ++p) {
             const long long r0 = 2 * p * kTileQ;
             if (2 * p + 1 < qt) {
-              emit_rows(c, r0, kTileQ);
-              emit_rows(c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ));
+              emit_rows(c, r0, kTileQ, kItemShared);
+              emit_rows(c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared);
             } else {                                           // odd last tile: two halves (the second may be empty)
               const long long r = m - r0, h = (r + 1) / 2;
-              emit_rows(c, r0, h);
-              emit_rows(c, r0 + h, r - h);
+              emit_rows(c, r0, h, kItemShared | kItemHalf);
+              emit_rows(c, r0 + h, r - h, kItemShared | kItemHalf);
             }
           }
       } else

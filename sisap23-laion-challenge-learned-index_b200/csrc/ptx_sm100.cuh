@@ -90,6 +90,12 @@ __device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// remote arrive with the default semantics (.release at CTA scope): enough when the data the barrier guards moves
+// through the async/tensor proxies (TMA, tcgen05) and is ordered by their own completion mechanisms; a
+// cluster-scope release costs a fence per arrive
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

@@ -113,7 +113,9 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_x);
     ptx::prefetch_tensormap(&tmap_xh);
-    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 2); }
+    // dbg_flags & 256 (experiment): no per-stage coupling between the two CTAs -- unicast loads only, a stage is
+    // retired by this CTA's own commit; the pair still starts and ends its work item together
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), (dbg_flags & 256) ? 1 : 2); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(ptx::smem_u32(&tfull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&tempty_bar[s]), 4); }
     ptx::mbar_init(ptx::smem_u32(afull_bar), 4);
     // item ring: the leader's producer publishes into both CTAs; its iempty collects the 6 local
@@ -133,6 +135,12 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
   if (blockIdx.x == 0 && threadIdx.x == 0) { clk0 = clock64(); ns0 = ptx::globaltimer_ns(); }
 
   // every consumer warp: next pair index from the ring, then release the slot to the leader
+  // dbg_flags & 512 (experiment): only lane 0 of a warp polls a per-tile barrier, the other 31 lanes park at __syncwarp
+  const bool poll_l0 = (dbg_flags & 512) != 0;
+  auto wait_w = [&](uint32_t bar, uint32_t parity) {
+    if (poll_l0) { if (lane == 0) ptx::mbar_wait(bar, parity); __syncwarp(); }
+    else ptx::mbar_wait(bar, parity);
+  };
   const uint32_t iempty_leader = ptx::mapa(ptx::smem_u32(iempty_bar), 0);
   auto next_pair = [&](int& islot, uint32_t& iphase) -> int {
     ptx::mbar_wait_cluster(ptx::smem_u32(&ifull_bar[islot]), iphase);
@@ -171,7 +179,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         const WorkItem wi = items[2 * pr + crank];
         const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
         const int n_tiles = (max(wi.obj_count, peer_count) + kTsBlockN - 1) / kTsBlockN;
-        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & 16);
+        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & (16 | 256));
         // L2 prefetch kTsPrefetch tiles ahead: the loads that fill the smem ring then see L2 latency,
         // not HBM latency (the ring holds ~1.6 tiles: 160 KB / 1.8 us of loaded HBM latency is only
         // 45 B/clk per SM, the MMA consumes 64 B/clk).  One CTA of a shared pair prefetches for both.
@@ -247,16 +255,16 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
           // always; longer rings only if TMA completions were reordered by three stages) -- observing the
           // phases makes the scheme independent of both.  The stages are full long before this warp's own.
           for (int ks = 0; ks < k_stages; ++ks) {
-            ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
+            wait_w(ptx::smem_u32(&full_bar[stage]), phase);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           continue;
         }
-        ptx::mbar_wait(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);
+        wait_w(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);
         ptx::tc_fence_after();
         for (int ks = 0; ks < k_stages; ++ks) {
           const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
-          ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
+          wait_w(ptx::smem_u32(&full_bar[stage]), phase);
           ptx::tc_fence_after();
           if (ptx::elect_one()) {
             const uint64_t b0 = ptx::umma_desc_k_sw128(ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes));
@@ -277,7 +285,8 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                                  b0 + (uint64_t)((i >> 2) * (kTsAtomBytes >> 4) + (i & 3) * 2), idesc,
                                  (ks | i) != 0 ? 1u : 0u);
             }
-            ptx::umma_commit_mc(ptx::smem_u32(&empty_bar[stage]), (uint16_t)3);   // stage retired here -> both CTAs' producers
+            if (dbg_flags & 256) ptx::umma_commit(ptx::smem_u32(&empty_bar[stage]));
+            else ptx::umma_commit_mc(ptx::smem_u32(&empty_bar[stage]), (uint16_t)3);   // stage retired here -> both CTAs' producers
             if (ks == k_stages - 1) ptx::umma_commit(ptx::smem_u32(&tfull_bar[parity]));   // accumulator complete
           }
           __syncwarp();
@@ -346,7 +355,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         }
         list.raise_seed(thr_decode(pending));
         __syncwarp();
-        ptx::mbar_wait(ptx::smem_u32(&tfull_bar[acc]), acc_phase);
+        wait_w(ptx::smem_u32(&tfull_bar[acc]), acc_phase);
         ptx::tc_fence_after();
         const uint32_t taddr = tmem_d + lane_addr + (uint32_t)(acc * kTsBlockN);
         const int pos0 = wi.obj_begin + col0;

@@ -77,15 +77,21 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
   const int n_pairs = sc->n_items >> 1;
   const int k_atoms = d / kTsAtomK;                                  // 12 for clip768
   const int k_stages = (k_atoms + kTsAtomsPerStage - 1) / kTsAtomsPerStage;
+  const bool relay = (dbg_flags & 16) != 0;
+  const bool cl_scope = (dbg_flags & 32) != 0;      // experiment: cluster-scope acquire/release on the per-tile barriers
+  auto wait_x = [&](uint32_t bar, uint32_t parity) { if (cl_scope) ptx::mbar_wait_cluster(bar, parity); else ptx::mbar_wait(bar, parity); };
+  auto arrive_x = [&](uint32_t cluster_addr) { if (cl_scope) ptx::mbar_arrive_cluster(cluster_addr); else ptx::mbar_arrive_remote(cluster_addr); };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_xh);
-    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 1); }
+    // relay mode (dbg_flags & 16, experiment): every CTA loads with the plain TMA form onto its OWN full barrier and
+    // the peer's otherwise idle warp 1 forwards each completed stage to the leader's barrier (second arrival)
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), (relay && crank == 0) ? 2 : 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), 1); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(ptx::smem_u32(&tfull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&tempty_bar[s]), 8); }
     ptx::mbar_init(ptx::smem_u32(afull_bar), 8);
     // item ring: the leader's iempty collects its 2 MMA + 4 epilogue warps and the peer's producer + 4
     // epilogue warps (the peer's MMA warps idle: only the leader issues)
-    for (int s = 0; s < kTsItemRing; ++s) { ptx::mbar_init(ptx::smem_u32(&ifull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&iempty_bar[s]), 11); }
+    for (int s = 0; s < kTsItemRing; ++s) { ptx::mbar_init(ptx::smem_u32(&ifull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&iempty_bar[s]), relay ? 12 : 11); }
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc2<512>(ptx::smem_u32(tmem_ptr));     // warp 1 of BOTH CTAs
@@ -143,11 +149,18 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
               if (++stage == STAGES) { stage = 0; phase ^= 1; }
               continue;
             }
-            if (crank == 0) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&full_bar[stage]), (uint32_t)(2 * atoms * kT2AtomBytes));
             const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kT2StageBytes);
-            const uint32_t fb = full_leader + (uint32_t)stage * 8u;
-            for (int a = 0; a < atoms; ++a)
-              ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+            if (relay) {
+              const uint32_t fbl = ptx::smem_u32(&full_bar[stage]);
+              ptx::mbar_arrive_expect_tx(fbl, (uint32_t)(atoms * kT2AtomBytes));
+              for (int a = 0; a < atoms; ++a)
+                ptx::tma_load_2d(sb + a * kT2AtomBytes, &tmap_xh, fbl, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+            } else {
+              if (crank == 0) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&full_bar[stage]), (uint32_t)(2 * atoms * kT2AtomBytes));
+              const uint32_t fb = full_leader + (uint32_t)stage * 8u;
+              for (int a = 0; a < atoms; ++a)
+                ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -161,7 +174,8 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
   } else if (warp == 1 || warp == 6) {
     // ===================== MMA issuers (leader CTA only; two warps alternate tiles) =====================
     if (crank == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * kTileQ, kTsBlockN);       // M = 256 over the pair, N = 64
+      constexpr uint32_t idesc_full = ptx::umma_idesc_f16(2 * kTileQ, kTsBlockN);  // M = 256 over the pair, N = 64
+      constexpr uint32_t idesc_half = ptx::umma_idesc_f16(kTileQ, kTsBlockN);      // M = 128 over the pair (64 rows per CTA)
       const int parity = (warp == 6) ? 1 : 0;
       const uint32_t d_tmem = tmem_d + (uint32_t)(parity * kTsBlockN);
       uint32_t g = 0;                                // running tile number; g & 1 = accumulator = issuing warp
@@ -172,7 +186,8 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         const int pr = next_pair(islot, iphase);
         if (pr >= n_pairs) break;
         const int n_tiles = (items[2 * pr].obj_count + kTsBlockN - 1) / kTsBlockN;
-        ptx::mbar_wait_cluster(ptx::smem_u32(afull_bar), a_phase);     // both CTAs' query rows are in tensor memory
+        const uint32_t idesc = (items[2 * pr].flags & kItemHalf) ? idesc_half : idesc_full;
+        wait_x(ptx::smem_u32(afull_bar), a_phase);     // both CTAs' query rows are in tensor memory
         a_phase ^= 1;
         for (int t = 0; t < n_tiles; ++t, ++g) {
           if ((int)(g & 1u) != parity) {
@@ -183,11 +198,11 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
             }
             continue;
           }
-          ptx::mbar_wait_cluster(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);   // drained in BOTH CTAs
+          wait_x(ptx::smem_u32(&tempty_bar[parity]), ((g >> 1) & 1u) ^ 1u);   // drained in BOTH CTAs
           ptx::tc_fence_after();
           for (int ks = 0; ks < k_stages; ++ks) {
             const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
-            ptx::mbar_wait_cluster(ptx::smem_u32(&full_bar[stage]), phase);         // both halves have landed
+            wait_x(ptx::smem_u32(&full_bar[stage]), phase);         // both halves have landed
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
               const uint64_t b0 = ptx::umma_desc_k_sw128(ptx::smem_u32(stage_base + (size_t)stage * kT2StageBytes));
@@ -215,6 +230,22 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
           }
         }
       }
+    } else if (relay && warp == 1) {
+      // peer CTA, relay mode: forward "my half of stage s has landed" to the leader's full barrier
+      const uint32_t full_leader = ptx::mapa(ptx::smem_u32(full_bar), 0);
+      int stage = 0; uint32_t phase = 0;
+      int islot = 0; uint32_t iphase = 0;
+      for (;;) {
+        const int pr = next_pair(islot, iphase);
+        if (pr >= n_pairs) break;
+        const int n_st = (items[2 * pr].obj_count + kTsBlockN - 1) / kTsBlockN * k_stages;
+        for (int i = 0; i < n_st; ++i) {
+          ptx::mbar_wait(ptx::smem_u32(&full_bar[stage]), phase);
+          if (lane == 0) arrive_x(full_leader + (uint32_t)stage * 8u);
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
     }
   } else {
     // ===================== epilogue (4 warps per CTA, thread = query row of this CTA's tile) =====================
@@ -231,8 +262,15 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
       const int pr = next_pair(islot, iphase);
       if (pr >= n_pairs) break;
       const WorkItem wi = items[2 * pr + crank];
-      const bool live = row < wi.rows && !(dbg_flags & 1);
-      const int qi = live ? slot_pair[wi.slot_base + row] / nb : -1;
+      // Half tile (kItemHalf, <= 64 rows per CTA, M = 128 pair MMAs): tensor memory lanes l and l + 64 both hold
+      // query row l & 63 ("duplicated" A layout); lanes 0-63 receive the scores of the tile's objects 0-31,
+      // lanes 64-127 those of objects 32-63 (accumulator columns 0-31 either way).  Threads l and l + 64 keep
+      // separate candidate lists over their halves of the objects, merged when the item ends.
+      const bool half = (wi.flags & kItemHalf) != 0;
+      const int qrow = half ? (row & 63) : row;
+      const int hoff = half ? (row >> 6) * (kTsBlockN / 2) : 0;
+      const bool live = qrow < wi.rows && !(dbg_flags & 1);
+      const int qi = live ? slot_pair[wi.slot_base + qrow] / nb : -1;
       // ---- this CTA's query rows -> its tensor memory (every MMA of the previous item has completed: this
       //      thread has seen the tfull barrier of its last tile, and that commit covers both CTAs) ----
       {
@@ -257,7 +295,7 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         ptx::tmem_st_wait();
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive_cluster(afull_leader);
+        if (lane == 0) arrive_x(afull_leader);
       }
       list.reset(l_sc, l_ps, row, live, live ? thr_decode(__ldcg(qthr + qi)) : kNegInf);
       const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
@@ -290,21 +328,25 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         // accumulator stage is in registers -> hand it back to the leader's MMA warp right away
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader + (uint32_t)acc * 8u);
+        if (lane == 0) arrive_x(tempty_leader + (uint32_t)acc * 8u);
         if (dbg_flags & 2) { if (++acc == 2) { acc = 0; acc_phase ^= 1; } continue; }   // experiment: nothing scored
         float s[kTsBlockN];
 #pragma unroll
         for (int c4 = 0; c4 < kTsBlockN / 4; ++c4) {
-          const float4 iv = *reinterpret_cast<const float4*>(inv + c4 * 4);
+          const float4 iv = *reinterpret_cast<const float4*>(inv + ((hoff + c4 * 4) & (kTsBlockN - 1)));
           const uint32_t* v = (c4 < 8) ? (v0 + c4 * 4) : (v1 + (c4 - 8) * 4);
           s[c4 * 4 + 0] = __uint_as_float(v[0]) * iv.x;
           s[c4 * 4 + 1] = __uint_as_float(v[1]) * iv.y;
           s[c4 * 4 + 2] = __uint_as_float(v[2]) * iv.z;
           s[c4 * 4 + 3] = __uint_as_float(v[3]) * iv.w;
         }
-        if (ncols != kTsBlockN) {
+        {
+          // columns past the chunk's end; half tile: only accumulator columns 0-31 exist, object = hoff + column
+          const int nvalid = half ? min(kTsBlockN / 2, ncols - hoff) : ncols;
+          if (nvalid != kTsBlockN) {
 #pragma unroll
-          for (int c = 0; c < kTsBlockN; ++c) if (c >= ncols) s[c] = kNegInf;
+            for (int c = 0; c < kTsBlockN; ++c) if (c >= nvalid) s[c] = kNegInf;
+          }
         }
         uint32_t gmask = 0u;
 #pragma unroll
@@ -319,7 +361,7 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
             if (gmask & (1u << g)) {
 #pragma unroll
               for (int j = 0; j < 8; ++j)
-                if (s[g * 8 + j] > list.thr) list.append(l_sc, l_ps, row, s[g * 8 + j], pos0 + g * 8 + j);
+                if (s[g * 8 + j] > list.thr) list.append(l_sc, l_ps, row, s[g * 8 + j], pos0 + hoff + g * 8 + j);
               if (__any_sync(0xffffffffu, list.cnt > kPend - 8)) list.prune(l_sc, l_ps, row);
             }
           }
@@ -330,8 +372,23 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
-      if (live)
+      if (half) {
+        // merge the list of thread l + 64 (objects 32-63 of every tile) into thread l's; named barrier over the
+        // four epilogue warps on both sides (lists complete / merge done before the next item resets them)
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (row < 64 && live) {
+#pragma unroll 1
+          for (int j = 0; j < KP; ++j) {
+            const float sv = l_sc[j * kTileQ + row + 64];
+            if (sv > list.lmin) list.insert_now(l_sc, l_ps, row, sv, l_ps[j * kTileQ + row + 64]);
+          }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (row < 64 && live)
+          list.flush(l_sc, l_ps, row, plists + (size_t)(wi.plist_base + (int64_t)row * wi.plist_stride) * KP);
+      } else if (live) {
         list.flush(l_sc, l_ps, row, plists + (size_t)(wi.plist_base + (int64_t)row * wi.plist_stride) * KP);
+      }
     }
   }
 

@@ -126,6 +126,21 @@ struct RowBuf {
     cnt = 0;
     thr = fmaxf(lmin, seed);
   }
+  // immediate insertion of one candidate that beats the list minimum (no pending entries; per-thread)
+  __device__ __forceinline__ void insert_now(float* sc, int32_t* ps, int row, float s, int32_t pos) {
+    sc[minpos * kTileQ + row] = s;
+    ps[minpos * kTileQ + row] = pos;
+    float m = sc[row];
+    int mp = 0;
+#pragma unroll 4
+    for (int j = 1; j < KP; ++j) {
+      const float v = sc[j * kTileQ + row];
+      if (v < m) { m = v; mp = j; }
+    }
+    lmin = m;
+    minpos = mp;
+    thr = fmaxf(lmin, seed);
+  }
   __device__ __forceinline__ void flush(const float* sc, const int32_t* ps, int row, Cand* out) const {
 #pragma unroll 4
     for (int j = 0; j < KP; ++j) {
