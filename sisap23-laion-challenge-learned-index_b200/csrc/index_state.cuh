@@ -82,6 +82,8 @@ struct lmi_index {
   CUtensorMap tmap_x64{};                   // store tensor map, box 64 x 64 (TS kernel)
   CUtensorMap tmap_xpf{};                   // store tensor map, box 64 x 256 unswizzled (TS kernel, L2 prefetch)
   CUtensorMap tmap_x32{};                   // store tensor map, box 32 x 64 (TS kernel, shared pairs)
+  CUtensorMap tmap_x3_64{}, tmap_x3_32{};     // 3-D views (64 halves, rows, K-atoms): one box = one pipeline stage
+  bool tmap_x3_ok = false;
   bool tmap_x_ok = false;
   int kernel_now = LMI_RESCORE_SIMT;         // kernel chosen for the search in flight
 

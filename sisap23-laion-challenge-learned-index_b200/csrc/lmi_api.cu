@@ -52,6 +52,24 @@ static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, int d, i
   return LMI_OK;
 }
 
+// The same [rows, d] fp16 matrix seen as a 3-D tensor (64 halves, rows, d/64 K-atoms): a box of
+// (64, box_rows, atoms) lands in shared memory as [atom][row][128 B] with the 128-byte swizzle -- exactly the
+// K-major UMMA operand layout of one pipeline stage -- so ONE cp.async.bulk.tensor fills a stage instead of
+// one per 64-half atom.
+static int make_tmap3(CUtensorMap* map, const void* base, uint64_t rows, int d, int box_rows, int box_atoms) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t gdim[3] = {64, (cuuint64_t)rows, (cuuint64_t)(d / 64)};
+  cuuint64_t gstride[2] = {(cuuint64_t)d * 2, 128};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, (cuuint32_t)box_atoms};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(LMI_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed, code " + std::to_string((int)r));
+  return LMI_OK;
+}
+
 }  // namespace lmi
 
 using namespace lmi;

@@ -14,6 +14,9 @@ static int launch_nav(lmi_index* idx, const float* x_dev, int64_t n, int n_top, 
 template <int KP>
 static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaStream_t st) {
   const int d = idx->d;
+  // Kernel bit 1024 = "fill a pipeline stage with ONE 3-D TMA box" (needs the 3-D tensor maps: d % 256 == 0).  It is
+  // the default; the option dbg_flags = 1024 turns it OFF (per-atom 2-D boxes, multicast for shared pairs).
+  const int dbg = idx->tmap_x3_ok ? (idx->dbg_flags ^ 1024) : (idx->dbg_flags & ~1024);
   bool done = false;
   if constexpr (KP <= 128) {
     if (idx->kernel_now == LMI_RESCORE_TC) {
@@ -27,9 +30,9 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
         LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done = true;
       }
-      kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x64, idx->tmap_x32, idx->tmap_xpf, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+      kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x64, idx->tmap_x32, idx->tmap_xpf, idx->tmap_x3_64, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                    idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
+                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), dbg);
       idx->rescore_name = "rescore_ts_kernel";
     }
   }
@@ -41,9 +44,9 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       auto launch = [&](auto kern, size_t smem) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+        kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, idx->tmap_x3_32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                           idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                          idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), idx->dbg_flags);
+                                                          idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), dbg);
         return cudaSuccess;
       };
       static_assert(ts2_smem_bytes<KP, STAGES>() <= 227 * 1024, "rescore_ts2: shared memory budget");

@@ -138,6 +138,11 @@ int lmi_store_end(lmi_index* idx) {
                                      std::min(idx->d, kTsAtomsPerStage * kTsAtomK), CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc != LMI_OK) return rc;
     idx->tmap_x_ok = true;
+    idx->tmap_x3_ok = false;
+    if (idx->d % (kTsAtomsPerStage * kTsAtomK) == 0 &&
+        make_tmap3(&idx->tmap_x3_64, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN, kTsAtomsPerStage) == LMI_OK &&
+        make_tmap3(&idx->tmap_x3_32, idx->x, (uint64_t)idx->n_local, idx->d, kTsBlockN / 2, kTsAtomsPerStage) == LMI_OK)
+      idx->tmap_x3_ok = true;
   }
   idx->store_open = false;
   idx->has_store = true;

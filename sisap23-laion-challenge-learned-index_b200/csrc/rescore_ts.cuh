@@ -79,6 +79,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTsThreads, 1)
 rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket store [n_local, d], box 64 x 64
                   const __grid_constant__ CUtensorMap tmap_xh,     // same, box 32 x 64 (half of a shared tile)
                   const __grid_constant__ CUtensorMap tmap_pf,     // same, box 64 x 256 unswizzled (L2 prefetch)
+                  const __grid_constant__ CUtensorMap tmap_x3,     // 3-D view, box 64 halves x 64 objects x 4 K-atoms = one stage
                   const uint16_t* __restrict__ q,                  // [nq, d] fp16 bits (original order)
                   const int32_t* __restrict__ slot_pair,           // slot -> pair index q*nb + r
                   int nb, int d, const float* __restrict__ inv_norm,
@@ -179,7 +180,8 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         const WorkItem wi = items[2 * pr + crank];
         const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
         const int n_tiles = (max(wi.obj_count, peer_count) + kTsBlockN - 1) / kTsBlockN;
-        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & (16 | 256));
+        const bool stage_box = (dbg_flags & 1024) != 0;      // one 3-D TMA per stage (needs d % 256 == 0; unicast only)
+        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & (16 | 256)) && !stage_box;
         // L2 prefetch kTsPrefetch tiles ahead: the loads that fill the smem ring then see L2 latency,
         // not HBM latency (the ring holds ~1.6 tiles: 160 KB / 1.8 us of loaded HBM latency is only
         // 45 B/clk per SM, the MMA consumes 64 B/clk).  One CTA of a shared pair prefetches for both.
@@ -203,7 +205,9 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
             }
             ptx::mbar_arrive_expect_tx(fb, (uint32_t)(atoms * kTsAtomBytes));
             const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kTsStageBytes);
-            if (shared) {
+            if (stage_box) {
+              ptx::tma_load_3d(sb, &tmap_x3, fb, 0, obj0, ks * kTsAtomsPerStage);
+            } else if (shared) {
               // this CTA fetches rows [32*crank, 32*crank+32) of the tile for both CTAs
               for (int a = 0; a < atoms; ++a)
                 ptx::tma_load_2d_mc(sb + a * kTsAtomBytes + crank * (kTsAtomBytes / 2), &tmap_xh, fb,

@@ -46,6 +46,7 @@ constexpr size_t ts2_smem_bytes() {
 template <int KP, int STAGES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTsThreads, 1)
 rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket store [n_local, d], box 32 x 64
+                   const __grid_constant__ CUtensorMap tmap_x3h,    // 3-D view, box 64 halves x 32 objects x 4 K-atoms = one stage
                    const uint16_t* __restrict__ q,                  // [nq, d] fp16 bits (original order)
                    const int32_t* __restrict__ slot_pair,           // slot -> pair index q*nb + r
                    int nb, int d, const float* __restrict__ inv_norm,
@@ -150,16 +151,21 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
               continue;
             }
             const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kT2StageBytes);
+            const bool stage_box = (dbg_flags & 1024) != 0;     // one 3-D TMA per stage (needs d % 256 == 0)
             if (relay) {
               const uint32_t fbl = ptx::smem_u32(&full_bar[stage]);
               ptx::mbar_arrive_expect_tx(fbl, (uint32_t)(atoms * kT2AtomBytes));
-              for (int a = 0; a < atoms; ++a)
-                ptx::tma_load_2d(sb + a * kT2AtomBytes, &tmap_xh, fbl, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+              if (stage_box) ptx::tma_load_3d(sb, &tmap_x3h, fbl, 0, obj0, ks * kTsAtomsPerStage);
+              else
+                for (int a = 0; a < atoms; ++a)
+                  ptx::tma_load_2d(sb + a * kT2AtomBytes, &tmap_xh, fbl, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
             } else {
               if (crank == 0) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&full_bar[stage]), (uint32_t)(2 * atoms * kT2AtomBytes));
               const uint32_t fb = full_leader + (uint32_t)stage * 8u;
-              for (int a = 0; a < atoms; ++a)
-                ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
+              if (stage_box) ptx::tma_load_3d_cg2(sb, &tmap_x3h, fb, 0, obj0, ks * kTsAtomsPerStage);
+              else
+                for (int a = 0; a < atoms; ++a)
+                  ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }

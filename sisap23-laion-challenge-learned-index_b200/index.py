@@ -18,6 +18,7 @@ the result definition.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -103,6 +104,8 @@ class GpuLearnedIndex:
         self._h = C.c_void_p()
         self.n_categories, self.d_nav, self.d, self.device = int(n_categories), int(d_nav), int(d), int(device)
         check(self._lib.lmi_create(C.byref(self._h), self.device, self.d_nav, self.d, self.n_categories))
+        if rescore == RESCORE_TC and os.environ.get("LMI_FORCE_PAIR_KERNEL", "0") == "1":
+            rescore = RESCORE_TC_PAIR            # test aid: run every default-kernel caller on the CTA-pair kernel
         self.set_option("rescore", rescore)
         if chunk_objects is not None:
             self.set_option("chunk_objects", chunk_objects)

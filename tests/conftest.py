@@ -54,3 +54,9 @@ def assert_ids_equal_up_to_ties(ids, dists, ref_ids, ref_dists, tie_eps=1e-12, w
             grp = np.where(np.abs(d - d[c]) <= tie_eps)[0]
             assert set(ids[r, grp].tolist()) == set(ref_ids[r, grp].tolist()), \
                 f"{what}: row {r} col {c}: ids {ids[r]} vs reference {ref_ids[r]} (dists {d})"
+
+
+# name(s) the default tcgen05 kernel may report: LMI_FORCE_PAIR_KERNEL=1 reroutes every default-kernel caller to the
+# CTA-pair kernel (lmi_b200.index), which is how the whole GPU suite is run against it
+import os as _os
+TS_KERNELS = ("rescore_ts2_kernel",) if _os.environ.get("LMI_FORCE_PAIR_KERNEL", "0") == "1" else ("rescore_ts_kernel",)

@@ -3,19 +3,15 @@
 golden vectors.  Every rescoring kernel hands the same survivors to the same float64 refine, so the
 final (dists, ids) must be BIT-IDENTICAL to the default kernel's.
 
-The kernel is experimental this round ("K3-pair"): these tests run only when
-``LMI_TEST_PAIR=1`` is set, so that the default ``-m gpu`` run covers exactly the shipped path.
+The kernel is opt-in this round ("K3-pair").  ``LMI_FORCE_PAIR_KERNEL=1`` additionally
+reroutes every default-kernel caller of the whole GPU suite to it (lmi_b200.index).
 """
-import os
-
 import numpy as np
 import pytest
 
 from conftest import load_golden, GOLDEN_TAGS, rows_with_small_buckets, assert_ids_equal_up_to_ties
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("LMI_TEST_PAIR", "0") != "1",
-                                 reason="experimental CTA-pair kernel: set LMI_TEST_PAIR=1")]
+pytestmark = pytest.mark.gpu
 
 PAIR = 3
 

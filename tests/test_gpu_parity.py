@@ -6,7 +6,7 @@ within 1e-12); distances within 1e-3 relative (BASELINE.json north_star) -- in p
 import numpy as np
 import pytest
 
-from conftest import load_golden, GOLDEN_TAGS, rows_with_small_buckets, assert_ids_equal_up_to_ties
+from conftest import load_golden, GOLDEN_TAGS, rows_with_small_buckets, assert_ids_equal_up_to_ties, TS_KERNELS
 
 pytestmark = pytest.mark.gpu
 
@@ -72,7 +72,7 @@ def test_search_matches_reference_clean(tag, rescore):
         st = li.stats()
         assert st["n_uncertified"] == 0, st
         assert st["max_abs_score_err"] < 5e-6, st
-        assert st["rescore_kernel"] == ["rescore_simt_kernel", "rescore_ts_kernel", "rescore_tc_kernel"][rescore]
+        assert st["rescore_kernel"] == ["rescore_simt_kernel", TS_KERNELS[0], "rescore_tc_kernel"][rescore]
 
 
 @pytest.mark.parametrize("tag", GOLDEN_TAGS)
