@@ -6,19 +6,21 @@
 // per-(rank, category) float64 cosine GEMM + argsort, search/li/LearnedIndex.py:143-172,
 // search/li/utils.py:10-11).  What changes is who holds the object tile:
 //
-//   rescore_ts  : every CTA receives the whole 64-object tile (96 KB per 128 x 64 x 768 tile = 64 B per
-//                 tensor-pipe cycle per SM); measured ingest 45 B/clk/SM -> ~2,450 cycles per tile
-//                 against 1,536 of MMA time.
+//   rescore_ts  : every CTA receives the whole 64-object tile (96 KB per 128 x 64 x 768 tile).
 //   rescore_ts2 : a work item is a PAIR of 128-query tiles of the same object chunk, one per CTA of a
 //                 2-CTA cluster.  One `tcgen05.mma.cta_group::2` (M = 256, N = 64, K = 16), issued by
 //                 the leader CTA, multiplies both query tiles (A: 128 rows in each CTA's tensor
 //                 memory) with a 64-object tile of which each CTA holds only ITS 32 objects in shared
 //                 memory.  Per SM and tile the MMA time is unchanged (32 cycles per instruction) but
-//                 the bytes that must arrive are halved: 48 KB per tile = 32 B/clk/SM.
+//                 the bytes that must arrive are halved (48 KB per tile), and one thread issues for
+//                 both SMs: MMA + handshake alone run at ~1,620 cycles per tile (floor 1,536) against
+//                 ~2,150 for the two lock-stepped CTAs of rescore_ts.
 //
 // Every tcgen05.alloc/mma/commit of a kernel must use one cta_group width, so this kernel cannot also
-// run single-CTA items: the planner's pair mode (plan.cuh, `pair_mode`) emits shared pairs only -- an odd
-// last query tile is split into two half tiles -- at the price of more padded MMA rows.
+// run single-CTA items: the planner's pair mode (plan.cuh, `pair_mode`) emits shared pairs only.  An odd
+// last query tile becomes two HALF tiles (<= 64 rows per CTA, kItemHalf) scored with M = 128 pair MMAs
+// (64 rows per CTA, half the tensor time): lanes l and l + 64 of a CTA's tensor memory hold query row
+// l & 63, lanes 0-63 receive the scores of the tile's objects 0-31, lanes 64-127 those of objects 32-63.
 //
 // Cross-CTA protocol (leader = cluster rank 0):
 //   full_bar[s]   (leader's)  : leader's producer expects the bytes of BOTH halves; the peer's TMA
