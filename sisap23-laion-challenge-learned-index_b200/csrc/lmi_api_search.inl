@@ -291,7 +291,6 @@ int lmi_search(lmi_index* idx, const float* q_nav, const uint16_t* q_f16, int64_
   int rc = run_search(idx, idx->ws_qnav.as<float>(), nullptr, idx->ws_q16.as<uint16_t>(), nq, n_buckets, k, nullptr, 0,
                       idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st, idx->ev_q16);
   if (rc != LMI_OK) { cudaStreamSynchronize(idx->copy_stream); return rc; }
-  if (rc != LMI_OK) return rc;
   LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
   LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
   LMI_CUDA(cudaStreamSynchronize(st));

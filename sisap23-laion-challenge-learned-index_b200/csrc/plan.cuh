@@ -155,11 +155,12 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
               emit_rows(c, r0 + h, r - h, kItemShared | kItemHalf);
             }
           }
-      } else
-      for (long long c0 = 0; c0 < ch; c0 += 2) {
-        for (long long c = c0; c < min(ch, c0 + 2); ++c)
-          for (long long p = 0; p < pairs_per_chunk; ++p) { emit(c, 2 * p, kItemShared); emit(c, 2 * p + 1, kItemShared); }
-        if (qt & 1) { emit(c0, qt - 1, 0); emit(c0 + 1 < ch ? c0 + 1 : -1, qt - 1, 0); }
+      } else {
+        for (long long c0 = 0; c0 < ch; c0 += 2) {
+          for (long long c = c0; c < min(ch, c0 + 2); ++c)
+            for (long long p = 0; p < pairs_per_chunk; ++p) { emit(c, 2 * p, kItemShared); emit(c, 2 * p + 1, kItemShared); }
+          if (qt & 1) { emit(c0, qt - 1, 0); emit(c0 + 1 < ch ? c0 + 1 : -1, qt - 1, 0); }
+        }
       }
     }
     __syncthreads();
