@@ -46,10 +46,10 @@ typedef enum {
 
 /* rescoring kernels (option "rescore") */
 #define LMI_RESCORE_SIMT 0    /* CUDA-core reference kernel (cross-check in tests) */
-#define LMI_RESCORE_TC   1    /* tcgen05 kernel, query tile resident in TMEM, objects streamed by TMA (default) */
+#define LMI_RESCORE_TC   1    /* tcgen05 kernel, query tile resident in TMEM, objects streamed by TMA (C-ABI default) */
 #define LMI_RESCORE_TC_SS 2   /* tcgen05 kernel, both operands streamed through shared memory (d > 768 fallback) */
 #define LMI_RESCORE_TC_PAIR 3 /* tcgen05 cta_group::2 kernel: query-tile pairs on 2-CTA clusters, each CTA holds half of
-                                 every object tile (experimental this round: opt-in) */
+                                 every object tile; what the Python host layer selects on an unsharded index */
 
 typedef struct {
   /* shape of the last search */
