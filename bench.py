@@ -374,7 +374,8 @@ def run_b200(args):
 
     # presharded: an ordinary (unsharded) index over this rank's rows; the exchange + merge are the same
     li = GpuLearnedIndex(args.categories, device=local_rank,
-                         rescore={"auto": None, "tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT, "tc_pair": RESCORE_TC_PAIR}[args.rescore],
+                         rescore={"auto": None if world == 1 else RESCORE_TC,      # multi-GPU runs (row-range shards included): single-CTA kernel
+                                  "tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT, "tc_pair": RESCORE_TC_PAIR}[args.rescore],
                          chunk_objects=args.chunk_objects, rank=0 if presharded else rank, world=1 if presharded else world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)
     li.set_model(inp["weights"], inp["biases"])
