@@ -77,6 +77,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, gpu_index=0, period=0.005):
         super().__init__(daemon=True)
         self.gpu, self.period, self.sm, self.reasons = gpu_index, period, [], set()
+        self.power_w = []
         self._stop_evt = threading.Event()
         self.max_mhz = None
         try:
@@ -91,6 +92,10 @@ class ClockSampler(threading.Thread):
     def _sample(self):
         nv = self.nv
         self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        try:
+            self.power_w.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+        except Exception:
+            pass
         try:
             r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
         except Exception:
@@ -113,8 +118,12 @@ class ClockSampler(threading.Thread):
     def stop(self):
         self._stop_evt.set()
         self.join(timeout=5)
-        return dict(sm_mhz=float(np.median(self.sm)) if self.sm else None, sm_max_mhz=self.max_mhz,
-                    reasons=sorted(self.reasons), samples=len(self.sm))
+        out = dict(sm_mhz=float(np.median(self.sm)) if self.sm else None, sm_max_mhz=self.max_mhz,
+                   reasons=sorted(self.reasons), samples=len(self.sm))
+        if self.power_w:          # board power while the timed region ran (the path is power-capped: DESIGN.md section 5)
+            out["power_w_median"] = float(np.median(self.power_w))
+            out["power_w_max"] = float(max(self.power_w))
+        return out
 
 
 # ----------------------------------------------------------------------------------------------
