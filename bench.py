@@ -46,7 +46,7 @@ def parse_args():
     p.add_argument("--blobs", type=int, default=2000)
     p.add_argument("--sigma", type=float, default=0.55)
     p.add_argument("--rescore", default="auto", choices=["auto", "tc", "tc_ss", "simt", "tc_pair"],
-                   help="auto = library default: tc_pair on an unsharded index, tc on a sharded one")
+                   help="auto = library default (tc_pair)")
     p.add_argument("--chunk-objects", type=int, default=None)
     p.add_argument("--shard", default="buckets", choices=["buckets", "stripes"])
     p.add_argument("--presharded", action="store_true",
@@ -383,7 +383,7 @@ def run_b200(args):
 
     # presharded: an ordinary (unsharded) index over this rank's rows; the exchange + merge are the same
     li = GpuLearnedIndex(args.categories, device=local_rank,
-                         rescore={"auto": None if world == 1 else RESCORE_TC,      # multi-GPU runs (row-range shards included): single-CTA kernel
+                         rescore={"auto": None,                                    # library default: CTA-pair tcgen05 kernel
                                   "tc": RESCORE_TC, "tc_ss": RESCORE_TC_SS, "simt": RESCORE_SIMT, "tc_pair": RESCORE_TC_PAIR}[args.rescore],
                          chunk_objects=args.chunk_objects, rank=0 if presharded else rank, world=1 if presharded else world,
                          shard_policy=SHARD_BUCKETS if args.shard == "buckets" else SHARD_STRIPES)

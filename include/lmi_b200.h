@@ -46,10 +46,10 @@ typedef enum {
 
 /* rescoring kernels (option "rescore") */
 #define LMI_RESCORE_SIMT 0    /* CUDA-core reference kernel (cross-check in tests) */
-#define LMI_RESCORE_TC   1    /* tcgen05 kernel, query tile resident in TMEM, objects streamed by TMA (C-ABI default) */
+#define LMI_RESCORE_TC   1    /* tcgen05 kernel, query tile resident in TMEM, objects streamed by TMA, one CTA per tile */
 #define LMI_RESCORE_TC_SS 2   /* tcgen05 kernel, both operands streamed through shared memory (d > 768 fallback) */
 #define LMI_RESCORE_TC_PAIR 3 /* tcgen05 cta_group::2 kernel: query-tile pairs on 2-CTA clusters, each CTA holds half of
-                                 every object tile; what the Python host layer selects on an unsharded index */
+                                 every object tile (default) */
 
 typedef struct {
   /* shape of the last search */
@@ -82,7 +82,7 @@ int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories);
 void lmi_destroy(lmi_index* idx);
 
 /* name/value tunables: "rescore" (LMI_RESCORE_*), "chunk_objects" (0 = chosen per search), "kprime_extra",
- * "timing" (1 = record per-stage CUDA events). */
+ * "epi_sets" (CTA-pair kernel: epilogue warp sets, 0 = automatic), "timing" (1 = record per-stage CUDA events). */
 int lmi_set_option(lmi_index* idx, const char* name, int64_t value);
 
 /* multi-GPU: this index holds shard `rank` of `world`.  Call before lmi_store_begin. */

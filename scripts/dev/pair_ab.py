@@ -70,7 +70,12 @@ def main():
     ap.add_argument("--seq", default="", help="explicit run sequence 'rescore:chunk:flags,...' (replaces the default A/B order; "
                                               "interleave variants -- the power-capped clock drifts over a process lifetime)")
     ap.add_argument("--dbg-pair-only", action="store_true", help="run the --dbg flags on the pair kernel only")
+    ap.add_argument("--exp", action="store_true", help="load liblmi_b200_exp.so (-DLMI_EXPERIMENTS build: dbg_flags honoured)")
     a = ap.parse_args()
+    if a.exp:
+        import lmi_b200.build as b
+        from lmi_b200 import _lib
+        _lib.LIB_PATH = b.build_experiments()
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     report = {}
     if not a.skip_diag:
@@ -100,11 +105,15 @@ def main():
     for f in [int(v) for v in a.dbg.split(",") if v != ""]:
         configs += [(3, 0, f)] if a.dbg_pair_only else [(1, 0, f), (3, 0, f)]
     if a.seq:
-        configs = [tuple(int(v) for v in item.split(":")) for item in a.seq.split(",")]
-    for rescore, chunk, flags in configs:
+        configs = [tuple(int(v) for v in item.split(":")) for item in a.seq.split(",")]       # rescore:chunk:flags[:epi_sets]
+    for cfg in configs:
+        rescore, chunk, flags = cfg[:3]
+        sets = cfg[3] if len(cfg) > 3 else 0
         li.set_option("rescore", rescore)
         li.set_option("chunk_objects", chunk)
-        li.set_option("dbg_flags", flags)
+        li.set_option("epi_sets", sets)
+        if a.exp or flags:
+            li.set_option("dbg_flags", flags)
         out = (torch.empty(nq, k, dtype=torch.float64, device=device), torch.empty(nq, k, dtype=torch.int32, device=device))
         for _ in range(3):
             li.search_device(qn, qs, nb, k, out)
@@ -121,7 +130,7 @@ def main():
         dd = out[0].cpu().numpy()
         if ref is None:
             ref = (dd, ids)
-        runs.append(dict(rescore=rescore, dbg_flags=flags, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
+        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
                          ms_per_search=ev0.elapsed_time(ev1) / a.steps, k3_ms_avg=st["ms_rescore_avg"],
                          k3_sm_mhz=st["k3_sm_mhz"], work_items=st["n_work_items"], pairs=st["pairs"],
                          padded_pairs=st["padded_pairs"], tile_efficiency=st["pairs"] / max(st["padded_pairs"], 1),

@@ -34,21 +34,46 @@ def is_stale() -> bool:
     return any(os.path.getmtime(s) > t for s in sources() if os.path.exists(s))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
-        return LIB_PATH
+# development-only twin with the kernels' experiment switches compiled in (-DLMI_EXPERIMENTS: option "dbg_flags",
+# results invalid by construction).  Used by scripts/dev only; the package never loads it.
+EXP_LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200_exp.so")
+
+
+def _stale(path) -> bool:
+    if not os.path.exists(path):
+        return True
+    t = os.path.getmtime(path)
+    return any(os.path.getmtime(s) > t for s in sources() if os.path.exists(s))
+
+
+def _nvcc(out_path, extra, verbose):
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
-        raise RuntimeError("nvcc not found: cannot build liblmi_b200.so")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB_PATH, os.path.join(CSRC, "lmi_api.cu")]
+        raise RuntimeError("nvcc not found: cannot build " + os.path.basename(out_path))
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", out_path, os.path.join(CSRC, "lmi_api.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
-    return LIB_PATH
+    return out_path
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not is_stale():
+        return LIB_PATH
+    return _nvcc(LIB_PATH, [], verbose)
+
+
+def build_experiments(force: bool = False, verbose: bool = False) -> str:
+    if not force and not _stale(EXP_LIB_PATH):
+        return EXP_LIB_PATH
+    return _nvcc(EXP_LIB_PATH, ["-DLMI_EXPERIMENTS"], verbose)
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--experiments" in sys.argv:
+        print(build_experiments(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

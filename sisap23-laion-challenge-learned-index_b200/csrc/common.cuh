@@ -6,6 +6,15 @@
 #include <stdio.h>
 #include <string>
 
+// Kernel experiments (switches that disable parts of a kernel; results invalid by construction) exist only in
+// builds made with -DLMI_EXPERIMENTS (scripts/dev); in the shipped library the tests below are constant false
+// and the branches disappear.
+#ifdef LMI_EXPERIMENTS
+#define LMI_DBG(flags, bit) (((flags) & (bit)) != 0)
+#else
+#define LMI_DBG(flags, bit) false
+#endif
+
 namespace lmi {
 
 constexpr float kNegInf = -3.0e38f;          // "empty" score in top-k' lists

@@ -52,11 +52,12 @@ struct lmi_index {
   cudaEvent_t ev_q16 = nullptr;
 
   // options
-  int rescore = LMI_RESCORE_TC;
+  int rescore = LMI_RESCORE_TC_PAIR;
   int chunk_objects = 0;                    // objects per work item; 0 = chosen per search (choose_chunk)
   int kprime_extra = 6;
   int timing = 1;
-  int dbg_flags = 0;                        // experiments only (bit 0: rescoring kernel never inserts)
+  int dbg_flags = 0;                        // kernel experiments; honoured by -DLMI_EXPERIMENTS builds only
+  int epi_sets = 0;                         // CTA-pair kernel: epilogue warp sets (0 = automatic: 2 while k' <= 32)
   int rank = 0, world = 1, policy = LMI_SHARD_BUCKETS;
 
   // model

@@ -144,8 +144,13 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   } else if (n == "kprime_extra") {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
     idx->kprime_extra = (int)value;
-  } else if (n == "dbg_flags") {
+  } else if (n == "epi_sets") {
+    if (value < 0 || value > 2) return set_error(LMI_ERR_ARG, "epi_sets: 0 (automatic), 1 or 2 epilogue warp sets in the CTA-pair kernel");
+    idx->epi_sets = (int)value;
+#ifdef LMI_EXPERIMENTS
+  } else if (n == "dbg_flags") {          // kernel experiments: scripts/dev builds only (results invalid when non-zero)
     idx->dbg_flags = (int)value;
+#endif
   } else if (n == "timing") {
     idx->timing = value ? 1 : 0;
   } else {
@@ -170,6 +175,8 @@ int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const flo
   LMI_CUDA(cudaSetDevice(idx->device));
   for (void* p : idx->mlp_allocs) cudaFree(p);
   idx->mlp_allocs.clear();
+  idx->has_mlp = false;           // until the new stack is complete: an error below must not leave pointers to freed weights
+  idx->layers = NavLayers{};
   NavLayers L{};
   L.n_layers = n_layers;
   L.max_width = idx->d_nav;
@@ -194,8 +201,7 @@ int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const flo
   }
   if (nav_smem_bytes(L) > 200 * 1024) return set_error(LMI_ERR_ARG, "MLP too wide for the navigation kernel (max width 800)");
   idx->layers = L;
-  idx->has_mlp = true;
-  LMI_CUDA(cudaFuncSetAttribute(nav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nav_smem_bytes(L)));
+  idx->has_mlp = true;            // (the shared-memory opt-in of nav_kernel is set at every launch: launch_nav)
   return LMI_OK;
 }
 

@@ -2,10 +2,19 @@
 
 namespace lmi {
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per function AND per device: it is set before every launch (a few
+// microseconds) instead of being cached per process, so a second index on another GPU, or another index with a
+// different shape, can never launch with a stale limit.
+template <class K>
+static cudaError_t opt_in_smem(K kern, size_t smem) {
+  return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
 static int launch_nav(lmi_index* idx, const float* x_dev, int64_t n, int n_top, int32_t* cls_dev, float* probs_dev,
                       cudaStream_t st) {
   if (n <= 0) return LMI_OK;
   const int64_t grid = (n + kNavTQ - 1) / kNavTQ;
+  LMI_CUDA(opt_in_smem(nav_kernel, nav_smem_bytes(idx->layers)));     // per device, and indexes with different MLPs share the function
   nav_kernel<<<(unsigned)grid, kNavThreads, nav_smem_bytes(idx->layers), st>>>(x_dev, n, idx->layers, n_top, cls_dev, probs_dev);
   LMI_CUDA(cudaGetLastError());
   return LMI_OK;
@@ -14,9 +23,12 @@ static int launch_nav(lmi_index* idx, const float* x_dev, int64_t n, int n_top, 
 template <int KP>
 static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaStream_t st) {
   const int d = idx->d;
-  // Kernel bit 1024 = "fill a pipeline stage with ONE 3-D TMA box" (needs the 3-D tensor maps: d % 256 == 0).  It is
-  // the default; the option dbg_flags = 1024 turns it OFF (per-atom 2-D boxes, multicast for shared pairs).
-  const int dbg = idx->tmap_x3_ok ? (idx->dbg_flags ^ 1024) : (idx->dbg_flags & ~1024);
+  const int stage_box = idx->tmap_x3_ok ? 1 : 0;      // one 3-D TMA box per pipeline stage (needs d % 256 == 0)
+#ifdef LMI_EXPERIMENTS
+  const int dbg = idx->dbg_flags;
+#else
+  const int dbg = 0;
+#endif
   bool done = false;
   if constexpr (KP <= 128) {
     if (idx->kernel_now == LMI_RESCORE_TC) {
@@ -25,32 +37,40 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       constexpr int STAGES = (KP <= 16) ? 5 : (KP <= 64) ? 4 : 2;
       auto kern = rescore_ts_kernel<KP, STAGES>;
       constexpr size_t smem = ts_smem_bytes<KP, STAGES>();
-      static bool attr_done = false;
-      if (!attr_done) {
-        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-      }
+      LMI_CUDA(opt_in_smem(kern, smem));
       kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x64, idx->tmap_x32, idx->tmap_xpf, idx->tmap_x3_64, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                    idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), dbg);
+                                                   idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), stage_box, dbg);
       idx->rescore_name = "rescore_ts_kernel";
     }
   }
   if constexpr (KP <= 128) {
     if (idx->kernel_now == LMI_RESCORE_TC_PAIR) {
       done = true;
-      // 16 KB stages per CTA (half tiles) beside the [k' + 16][128] x 8 B candidate lists
-      constexpr int STAGES = (KP <= 32) ? 10 : (KP <= 64) ? 8 : 4;
-      auto launch = [&](auto kern, size_t smem) -> cudaError_t {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      auto launch = [&](auto kern, size_t smem, int threads) -> cudaError_t {
+        cudaError_t e = opt_in_smem(kern, smem);
         if (e != cudaSuccess) return e;
-        kern<<<idx->num_sms & ~1, kTsThreads, smem, st>>>(idx->tmap_x32, idx->tmap_x3_32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
-                                                          idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                          idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), dbg);
+        kern<<<idx->num_sms & ~1, threads, smem, st>>>(idx->tmap_x32, idx->tmap_x3_32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
+                                                       idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
+                                                       idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), stage_box, dbg);
         return cudaSuccess;
       };
-      static_assert(ts2_smem_bytes<KP, STAGES>() <= 227 * 1024, "rescore_ts2: shared memory budget");
-      LMI_CUDA(launch(rescore_ts2_kernel<KP, STAGES>, ts2_smem_bytes<KP, STAGES>()));
+      // 16 KB stages per CTA (half tiles) beside SETS x [k' + 16][128] x 8 B candidate lists.  Two epilogue warp
+      // sets (one per accumulator) while their lists fit: k' <= 32; option "epi_sets" = 1 forces one set.
+      bool two_sets = false;
+      if constexpr (KP <= 32) {
+        if (idx->epi_sets != 1) {
+          two_sets = true;
+          constexpr int STAGES = (KP <= 16) ? 9 : 7;
+          static_assert(ts2_smem_bytes<KP, STAGES, 2>() <= 227 * 1024, "rescore_ts2 (2 sets): shared memory budget");
+          LMI_CUDA(launch(rescore_ts2_kernel<KP, STAGES, 2>, ts2_smem_bytes<KP, STAGES, 2>(), ts2_threads(2)));
+        }
+      }
+      if (!two_sets) {
+        constexpr int STAGES = (KP <= 32) ? 10 : (KP <= 64) ? 8 : 4;
+        static_assert(ts2_smem_bytes<KP, STAGES, 1>() <= 227 * 1024, "rescore_ts2: shared memory budget");
+        LMI_CUDA(launch(rescore_ts2_kernel<KP, STAGES, 1>, ts2_smem_bytes<KP, STAGES, 1>(), ts2_threads(1)));
+      }
       idx->rescore_name = "rescore_ts2_kernel";
     }
   }
@@ -60,11 +80,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
       constexpr int STAGES = (KP <= 16) ? 4 : 3;
       auto kern = rescore_tc_kernel<KP, STAGES>;
       constexpr size_t smem = tc_smem_bytes<KP, STAGES>();
-      static bool attr_done = false;
-      if (!attr_done) {
-        LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-      }
+      LMI_CUDA(opt_in_smem(kern, smem));
       kern<<<idx->num_sms, kTcThreads, smem, st>>>(idx->tmap_q, idx->tmap_x, d, idx->inv_norm, idx->items.as<WorkItem>(),
                                                    idx->scalars.as<PlanScalars>(), idx->plists.as<Cand>());
       idx->rescore_name = "rescore_tc_kernel";
@@ -73,11 +89,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
   if (!done) {
     auto kern = rescore_simt_kernel<KP>;
     constexpr size_t smem = simt_smem_bytes<KP>();
-    static bool attr_done = false;
-    if (!attr_done) {
-      LMI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_done = true;
-    }
+    LMI_CUDA(opt_in_smem(kern, smem));
     kern<<<idx->num_sms * 2, kTileQ, smem, st>>>(q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->x, idx->inv_norm,
                                                  idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
                                                  idx->plists.as<Cand>());

@@ -96,6 +96,12 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// remote arrive without any ordering (no fence at all): for barriers whose guarded resource is handed over by an
+// already-completed tcgen05 operation (e.g. "accumulator drained": tcgen05.wait::ld has returned, the values are in
+// registers).  The .release forms above compile to MEMBAR.ALL.GPU + CGAERRBAR on a shared::cluster address.
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -110,6 +116,10 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t par
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait_cluster(bar, parity)) { }
 }
+
+// register re-allocation between warpgroups (all warps of the warpgroup execute it)
+template <uint32_t kRegs> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs)); }
+template <uint32_t kRegs> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs)); }
 
 // ---- TMA -----------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* m) {

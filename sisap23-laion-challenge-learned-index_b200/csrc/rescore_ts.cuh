@@ -85,7 +85,9 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                   int nb, int d, const float* __restrict__ inv_norm,
                   const WorkItem* __restrict__ items, PlanScalars* __restrict__ sc,
                   uint32_t* __restrict__ qthr,                     // [nq] shared per-query threshold
-                  Cand* __restrict__ plists, int dbg_flags) {
+                  Cand* __restrict__ plists,
+                  int stage_box_arg,                               // 1: one 3-D TMA box fills a stage (d % 256 == 0; unicast)
+                  int dbg_flags) {                                 // experiments (LMI_EXPERIMENTS builds only)
   extern __shared__ unsigned char ts_smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
   // (offset arithmetic on the shared array keeps the shared address space visible to the compiler)
@@ -116,7 +118,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
     ptx::prefetch_tensormap(&tmap_xh);
     // dbg_flags & 256 (experiment): no per-stage coupling between the two CTAs -- unicast loads only, a stage is
     // retired by this CTA's own commit; the pair still starts and ends its work item together
-    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), (dbg_flags & 256) ? 1 : 2); }
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(ptx::smem_u32(&full_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&empty_bar[s]), LMI_DBG(dbg_flags, 256) ? 1 : 2); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(ptx::smem_u32(&tfull_bar[s]), 1); ptx::mbar_init(ptx::smem_u32(&tempty_bar[s]), 4); }
     ptx::mbar_init(ptx::smem_u32(afull_bar), 4);
     // item ring: the leader's producer publishes into both CTAs; its iempty collects the 6 local
@@ -137,7 +139,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
 
   // every consumer warp: next pair index from the ring, then release the slot to the leader
   // dbg_flags & 512 (experiment): only lane 0 of a warp polls a per-tile barrier, the other 31 lanes park at __syncwarp
-  const bool poll_l0 = (dbg_flags & 512) != 0;
+  const bool poll_l0 = LMI_DBG(dbg_flags, 512);
   auto wait_w = [&](uint32_t bar, uint32_t parity) {
     if (poll_l0) { if (lane == 0) ptx::mbar_wait(bar, parity); __syncwarp(); }
     else ptx::mbar_wait(bar, parity);
@@ -180,12 +182,12 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         const WorkItem wi = items[2 * pr + crank];
         const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
         const int n_tiles = (max(wi.obj_count, peer_count) + kTsBlockN - 1) / kTsBlockN;
-        const bool stage_box = (dbg_flags & 1024) != 0;      // one 3-D TMA per stage (needs d % 256 == 0; unicast only)
-        const bool shared = (wi.flags & kItemShared) != 0 && !(dbg_flags & (16 | 256)) && !stage_box;
+        const bool stage_box = stage_box_arg != 0;
+        const bool shared = (wi.flags & kItemShared) != 0 && !LMI_DBG(dbg_flags, 16 | 256) && !stage_box;
         // L2 prefetch kTsPrefetch tiles ahead: the loads that fill the smem ring then see L2 latency,
         // not HBM latency (the ring holds ~1.6 tiles: 160 KB / 1.8 us of loaded HBM latency is only
         // 45 B/clk per SM, the MMA consumes 64 B/clk).  One CTA of a shared pair prefetches for both.
-        const bool do_pf = (dbg_flags & 32) && (!shared || crank == 0);   // measured: no gain on B200 (kept as an experiment)
+        const bool do_pf = LMI_DBG(dbg_flags, 32) && (!shared || crank == 0);   // measured: no gain on B200 (kept as an experiment)
         auto prefetch_tile = [&](int t) {
           for (int ks = 0; ks < k_stages; ++ks)
             ptx::tma_prefetch_2d(&tmap_pf, ks * kTsAtomsPerStage * kTsAtomK, wi.obj_begin + t * kTsBlockN);
@@ -198,7 +200,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
             const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
             ptx::mbar_wait(ptx::smem_u32(&empty_bar[stage]), phase ^ 1);    // retired by BOTH CTAs
             const uint32_t fb = ptx::smem_u32(&full_bar[stage]);
-            if (dbg_flags & 4) {                                     // experiment: no loads at all
+            if (LMI_DBG(dbg_flags, 4)) {                             // experiment: no loads at all
               ptx::mbar_arrive(fb);
               if (++stage == STAGES) { stage = 0; phase ^= 1; }
               continue;
@@ -275,7 +277,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
             const uint32_t a0 = tmem_base + (uint32_t)(ks * kTsAtomsPerStage * 32);   // 32 columns per atom
             // A: 16 halves = 8 TMEM columns per K=16 slice; B: +32 bytes inside the swizzle span
             // (+2 in the addr>>4 field), next atom +8 KB (+512)
-            if (dbg_flags & 8) {
+            if (LMI_DBG(dbg_flags, 8)) {
             } else if (atoms == kTsAtomsPerStage) {
               if (ks == 0) ptx::umma_f16_ts_c<false>(d_tmem, a0, b0, idesc);
               else         ptx::umma_f16_ts_c<true>(d_tmem, a0, b0, idesc);
@@ -289,7 +291,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
                                  b0 + (uint64_t)((i >> 2) * (kTsAtomBytes >> 4) + (i & 3) * 2), idesc,
                                  (ks | i) != 0 ? 1u : 0u);
             }
-            if (dbg_flags & 256) ptx::umma_commit(ptx::smem_u32(&empty_bar[stage]));
+            if (LMI_DBG(dbg_flags, 256)) ptx::umma_commit(ptx::smem_u32(&empty_bar[stage]));
             else ptx::umma_commit_mc(ptx::smem_u32(&empty_bar[stage]), (uint16_t)3);   // stage retired here -> both CTAs' producers
             if (ks == k_stages - 1) ptx::umma_commit(ptx::smem_u32(&tfull_bar[parity]));   // accumulator complete
           }
@@ -312,7 +314,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
       if (pr >= n_pairs) break;
       const WorkItem wi = items[2 * pr + crank];
       const int peer_count = items[2 * pr + (crank ^ 1)].obj_count;
-      const bool live = row < wi.rows && !(dbg_flags & 1);
+      const bool live = row < wi.rows && !LMI_DBG(dbg_flags, 1);
       const int qi = live ? slot_pair[wi.slot_base + row] / nb : -1;
       // ---- the item's query rows -> TMEM (all MMAs of the previous item have completed: this
       //      thread has seen the tfull barrier of its last tile) ----
@@ -375,7 +377,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
         // multiplies of all groups overlap), then the rare paths.  A group of 8 columns is entered only
         // if some row of the warp has a candidate in it (warp-uniform branch; the append path must
         // not be if-converted into the hot loop).
-        if (dbg_flags & 2) { if (++acc == 2) { acc = 0; acc_phase ^= 1; } continue; }   // experiment: accumulator drained, nothing scored
+        if (LMI_DBG(dbg_flags, 2)) { if (++acc == 2) { acc = 0; acc_phase ^= 1; } continue; }   // experiment: accumulator drained, nothing scored
         float s[kTsBlockN];
 #pragma unroll
         for (int c4 = 0; c4 < kTsBlockN / 4; ++c4) {
@@ -410,7 +412,7 @@ rescore_ts_kernel(const __grid_constant__ CUtensorMap tmap_x,      // bucket sto
           }
         }
         // publish this row's bound / pick up the other CTAs' (the atomic's old value is read next tile)
-        if (dbg_flags & 64) { if (__any_sync(0xffffffffu, list.cnt >= 3)) list.prune(l_sc, l_ps, row); }
+        if (LMI_DBG(dbg_flags, 64)) { if (__any_sync(0xffffffffu, list.cnt >= 3)) list.prune(l_sc, l_ps, row); }
         if ((t + 1) % kTsRefresh == 0 || t + 1 == n_tiles) {
           list.prune(l_sc, l_ps, row);
           if (live) pending = atomicMax(qthr + qi, list.lmin > kNegInf ? thr_encode(list.lmin) : 0u);

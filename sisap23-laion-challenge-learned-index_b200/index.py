@@ -105,13 +105,14 @@ class GpuLearnedIndex:
         self.n_categories, self.d_nav, self.d, self.device = int(n_categories), int(d_nav), int(d), int(device)
         check(self._lib.lmi_create(C.byref(self._h), self.device, self.d_nav, self.d, self.n_categories))
         if rescore is None:
-            # default: the CTA-pair tcgen05 kernel on an unsharded clip768 index (validated on the whole GPU suite and the
-            # 10M bench, +6 %); sharded indexes keep the single-CTA kernel until the pair kernel has been run
-            # on real multi-GPU boxes.  LMI_RESCORE=<0..3> overrides.
+            # default: the CTA-pair tcgen05 kernel, sharded or not; the library falls back
+            # to the smem-operand / CUDA-core kernels for shapes it does not cover (d > 768).  LMI_RESCORE=<0..3> overrides.
             env = os.environ.get("LMI_RESCORE", "")
-            rescore = int(env) if env != "" else (RESCORE_TC_PAIR if (world == 1 and self.d == 768) else RESCORE_TC)
+            if env != "" and env not in ("0", "1", "2", "3"):
+                raise ValueError(f"LMI_RESCORE must be 0..3, got {env!r}")
+            rescore = int(env) if env != "" else RESCORE_TC_PAIR
         if rescore == RESCORE_TC and os.environ.get("LMI_FORCE_PAIR_KERNEL", "0") == "1":
-            rescore = RESCORE_TC_PAIR            # test aid: run every default-kernel caller on the CTA-pair kernel
+            rescore = RESCORE_TC_PAIR            # test aid: run every single-CTA-kernel caller on the CTA-pair kernel
         self.set_option("rescore", rescore)
         if chunk_objects is not None:
             self.set_option("chunk_objects", chunk_objects)

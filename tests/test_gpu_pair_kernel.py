@@ -70,11 +70,17 @@ def _search(li, c, nb, k):
     return li.search(None, c["queries_nav"], c["data_f16"], c["queries_f16"], c["pred_categories"], n_buckets=nb, k=k)
 
 
-@pytest.mark.parametrize("nb,k,chunk", [(1, 10, 0), (4, 10, 0), (7, 10, 0), (4, 10, 512), (48, 10, 256),
+@pytest.mark.parametrize("sets", [1, 2], ids=["1set", "2sets"])
+@pytest.mark.parametrize("nb,k,chunk", [(1, 10, 0), (4, 10, 0), (7, 10, 0), (4, 10, 512), (48, 10, 256), (4, 20, 320),
                                         (3, 50, 0), (2, 100, 0), (2, 100, 1024)])
-def test_pair_kernel_equals_default_kernel(case, nb, k, chunk):
+def test_pair_kernel_equals_default_kernel(case, nb, k, chunk, sets):
+    """`sets`: epilogue warp sets of the pair kernel (option "epi_sets"; two sets exist for k' <= 32, larger k'
+    always run one), each with its own per-row candidate list merged in shared memory at the end of an item."""
     c = case
+    if sets == 2 and k + 6 > 32:
+        pytest.skip("two epilogue sets exist for k' <= 32 only")
     li3 = _index(c, PAIR, chunk_objects=chunk)
+    li3.set_option("epi_sets", sets)
     d3, a3 = _search(li3, c, nb, k)
     st = li3.stats()
     assert st["rescore_kernel"] == "rescore_ts2_kernel" and st["n_uncertified"] == 0, st
