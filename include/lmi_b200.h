@@ -104,7 +104,19 @@ int lmi_store_begin(lmi_index* idx, const int64_t* pred_categories, int64_t n_to
  * may be called in any order / chunking until every row was seen once. */
 int lmi_store_append(lmi_index* idx, const uint16_t* rows_f16, int64_t first_row, int64_t rows,
                      int on_device);
+/* same for a strided source: element (r, c) of the chunk lies at base[r * row_stride + c * col_stride] (strides in
+ * ELEMENTS).  Row-major rows (col_stride = 1, row_stride >= d) or feature-major columns (row_stride = 1,
+ * col_stride >= rows: how pandas lays out the block of a DataFrame built as search.py:83-84 builds data_search, so
+ * it is uploaded as it lies instead of being transposed on the host).  Host sources go through two pinned staging
+ * buffers, overlapping the host-side gather with the H2D copy. */
+int lmi_store_append_strided(lmi_index* idx, const uint16_t* base, int64_t first_row, int64_t rows,
+                             int64_t row_stride, int64_t col_stride, int on_device);
 int lmi_store_end(lmi_index* idx);
+/* on-disk cache of the finished device layout (CSR fp16 rows + inverse norms + ids) of this index / shard.
+ * key32: 32 bytes chosen by the caller (a hash of pred_categories and a fingerprint of the data) stored in the
+ * file and compared on load; lmi_store_load fails with LMI_ERR_STATE on any mismatch (shape, shard, key). */
+int lmi_store_save(lmi_index* idx, const char* path, const uint8_t* key32);
+int lmi_store_load(lmi_index* idx, const char* path, const uint8_t* key32);
 /* convenience: begin + append(all) + end from host memory */
 int lmi_set_buckets(lmi_index* idx, const uint16_t* data_f16, const int64_t* pred_categories,
                     int64_t n_total, int64_t id_base);

@@ -83,6 +83,25 @@ def run_reference_case(tag, n, nq, n_categories, model_type, epochs, bucket_list
         out[f"shipped_dists_nb{nb}"], out[f"shipped_ids_nb{nb}"] = d, a
         out[f"shipped_d1_nb{nb}"] = fl.flags.copy()
 
+    # the threshold path of search_single exactly as search() drives it for rank 1 (LearnedIndex.py:71-81,
+    # :149-163 -> utils.py:14-43): categories = classes[:, 1], threshold = the k-th distance after rank 0.
+    # Slots whose distance is 10000.0 carry arbitrary ids (utils.py:33-42 pads the compact matrix), rows that
+    # went through the '<k' branch (D1) are flagged; consumers compare ids on slots with dist < 10000 of
+    # unflagged rows.
+    thr = d1.max(axis=1)
+    with ref_shims.D1Flagger(nq, k) as fl:
+        dt, at = li.search_single(data_navigation=nav_copy, data_search=data_search, queries_search=q_f16,
+                                  pred_categories=classes[:, 1], k=k, threshold_dist=thr)
+    out["single_thr"], out["single_thr_dists"], out["single_thr_ids"] = thr, dt, at
+    out["single_thr_d1"] = fl.flags.copy()
+    # a tighter threshold (median of the rank-0 distances) on rank 0's own categories: most slots are pruned
+    thr2 = np.median(d1, axis=1)
+    with ref_shims.D1Flagger(nq, k) as fl2:
+        dt2, at2 = li.search_single(data_navigation=nav_copy, data_search=data_search, queries_search=q_f16,
+                                    pred_categories=classes[:, 0], k=k, threshold_dist=thr2)
+    out["single_thr2"], out["single_thr2_dists"], out["single_thr2_ids"] = thr2, dt2, at2
+    out["single_thr2_d1"] = fl2.flags.copy()
+
     # brute-force ground truth from the reference's own Baseline (Baseline.py:14-20)
     sub = min(64, nq)
     bd, bi, _ = ref.baseline.Baseline().search(queries=q_f16[:sub], data=arrs["data_f16"], k=k)

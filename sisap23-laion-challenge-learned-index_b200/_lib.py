@@ -14,7 +14,8 @@ LIB_PATH = os.path.join(PKG_DIR, "liblmi_b200.so")
 # every symbol include/lmi_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "lmi_last_error", "lmi_version", "lmi_create", "lmi_destroy", "lmi_set_option", "lmi_set_shard",
-    "lmi_set_mlp", "lmi_store_begin", "lmi_store_append", "lmi_store_end", "lmi_set_buckets",
+    "lmi_set_mlp", "lmi_store_begin", "lmi_store_append", "lmi_store_append_strided",
+    "lmi_store_end", "lmi_store_save", "lmi_store_load", "lmi_set_buckets",
     "lmi_navigate", "lmi_predict", "lmi_search", "lmi_search_device", "lmi_search_rank",
     "lmi_partial_bytes", "lmi_search_partial_device", "lmi_merge_partials_device", "lmi_get_stats",
     "lmi_get_bucket_ptr", "lmi_rescore_kernel_name",
@@ -63,6 +64,9 @@ def load() -> C.CDLL:
     lib.lmi_set_mlp.argtypes = [p, i, C.POINTER(C.c_int32), C.POINTER(vp), C.POINTER(vp)]
     lib.lmi_store_begin.argtypes = [p, vp, i64, i64, i]
     lib.lmi_store_append.argtypes = [p, vp, i64, i64, i]
+    lib.lmi_store_append_strided.argtypes = [p, vp, i64, i64, i64, i64, i]
+    lib.lmi_store_save.argtypes = [p, C.c_char_p, C.c_char_p]
+    lib.lmi_store_load.argtypes = [p, C.c_char_p, C.c_char_p]
     lib.lmi_store_end.argtypes = [p]
     lib.lmi_set_buckets.argtypes = [p, vp, vp, i64, i64]
     lib.lmi_navigate.argtypes = [p, vp, i64, i, vp, vp]

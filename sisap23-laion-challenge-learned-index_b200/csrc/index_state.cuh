@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <string.h>
 #include <algorithm>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -41,6 +42,20 @@ struct DevBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// grow-only pinned host buffer
+struct PinBuf {
+  void* p = nullptr; size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+    cudaError_t e = cudaMallocHost(&p, bytes + bytes / 8 + 256);
+    if (e == cudaSuccess) cap = bytes + bytes / 8 + 256;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+
 }  // namespace lmi
 
 struct lmi_index {
@@ -70,7 +85,10 @@ struct lmi_index {
   int64_t n_total = 0, n_local = 0, id_base = 1;
   int64_t rows_seen = 0;
   lmi::DevBuf cats, pos, block_hist, bucket_size, keep_lo, keep_hi, owner, bucket_ptr;   // build-time
-  lmi::DevBuf stage_rows;                                                                // host->device staging
+  lmi::DevBuf stage_rows, stage_rows_t;                                                  // host->device staging (row-major / feature-major)
+  void* pin_stage[2] = {nullptr, nullptr};  // pinned host staging (double-buffered upload), freed by lmi_store_end
+  cudaEvent_t pin_ev[2] = {nullptr, nullptr};
+  std::vector<int64_t> h_global_sizes;      // bucket sizes over ALL ranks (set by lmi_store_begin)
   uint16_t* x = nullptr;                    // [n_local, d] fp16, CSR by bucket
   float* inv_norm = nullptr;                // [n_local]
   uint32_t* ids = nullptr;                  // [n_local]
@@ -90,6 +108,7 @@ struct lmi_index {
 
   // search workspace (grow-only)
   lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;
+  lmi::PinBuf pin_in, pin_out;               // staging for pageable caller buffers (lmi_search / lmi_search_rank)
   lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr;
   lmi::DevBuf nav_cls, nav_probs, nav_x;
   CUtensorMap tmap_q{};

@@ -117,12 +117,14 @@ void lmi_destroy(lmi_index* idx) {
                     &idx->owner, &idx->bucket_ptr, &idx->stage_rows, &idx->ws_qnav, &idx->ws_q16, &idx->ws_out_d,
                     &idx->ws_out_i, &idx->ws_thr, &idx->ws_cls64, &idx->top_cls, &idx->m_b, &idx->qoff,
                     &idx->chunks_b, &idx->plist_base, &idx->slot_pair, &idx->pair_slot, &idx->items, &idx->plists,
-                    &idx->qg, &idx->scalars, &idx->qthr, &idx->nav_cls, &idx->nav_probs, &idx->nav_x};
+                    &idx->qg, &idx->scalars, &idx->qthr, &idx->nav_cls, &idx->nav_probs, &idx->nav_x, &idx->stage_rows_t};
   for (DevBuf* b : bufs) b->release();
   if (idx->x) cudaFree(idx->x);
   if (idx->inv_norm) cudaFree(idx->inv_norm);
   if (idx->ids) cudaFree(idx->ids);
+  idx->pin_in.release(); idx->pin_out.release();
   if (idx->h_scalars) cudaFreeHost(idx->h_scalars);
+  for (int b = 0; b < 2; ++b) { if (idx->pin_stage[b]) cudaFreeHost(idx->pin_stage[b]); if (idx->pin_ev[b]) cudaEventDestroy(idx->pin_ev[b]); }
   for (auto& e : idx->ev) if (e) cudaEventDestroy(e);
   for (auto& pr : idx->ev_k3) for (auto& e : pr) if (e) cudaEventDestroy(e);
   if (idx->stream) cudaStreamDestroy(idx->stream);

@@ -2,6 +2,30 @@
 
 namespace lmi {
 
+// Host -> device copy of a caller buffer on `st`.  Pinned (or registered) memory goes straight to cudaMemcpyAsync;
+// PAGEABLE memory -- what numpy hands the drop-in search() -- is first gathered into a pinned staging buffer by a few
+// host threads (the driver's own pageable path is a single-threaded staged copy and blocks the caller for ~2 ms at
+// the 15 MB of a 10k-query batch).  `pin` is a grow-only pinned buffer owned by the index.
+static bool host_ptr_is_pinned(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const int n_thr = (int)std::min<size_t>(std::min(8u, hw), bytes / ((size_t)1 << 20) + 1);
+  if (n_thr <= 1) { memcpy(dst, src, bytes); return; }
+  std::vector<std::thread> pool;
+  auto work = [&](int t) {
+    const size_t lo = bytes * t / n_thr / 64 * 64, hi = (t + 1 == n_thr) ? bytes : bytes * (t + 1) / n_thr / 64 * 64;
+    memcpy((char*)dst + lo, (const char*)src + lo, hi - lo);
+  };
+  for (int t = 1; t < n_thr; ++t) pool.emplace_back(work, t);
+  work(0);
+  for (auto& th : pool) th.join();
+}
+
 // cudaFuncAttributeMaxDynamicSharedMemorySize is per function AND per device: it is set before every launch (a few
 // microseconds) instead of being cached per process, so a second index on another GPU, or another index with a
 // different shape, can never launch with a stale limit.
@@ -241,6 +265,24 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   return LMI_OK;
 }
 
+// results -> caller buffers (through pinned staging when the caller's are pageable), synchronous on return
+static int copy_results_out(lmi_index* idx, int64_t nq, int k, double* out_dists, uint32_t* out_ids, cudaStream_t st) {
+  const size_t b_d = (size_t)nq * k * 8, b_i = (size_t)nq * k * 4;
+  if (host_ptr_is_pinned(out_dists) && host_ptr_is_pinned(out_ids)) {
+    LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, b_d, cudaMemcpyDeviceToHost, st));
+    LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, b_i, cudaMemcpyDeviceToHost, st));
+    LMI_CUDA(cudaStreamSynchronize(st));
+    return LMI_OK;
+  }
+  LMI_CUDA(idx->pin_out.reserve(b_d + b_i));
+  LMI_CUDA(cudaMemcpyAsync(idx->pin_out.p, idx->ws_out_d.p, b_d, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaMemcpyAsync((char*)idx->pin_out.p + b_d, idx->ws_out_i.p, b_i, cudaMemcpyDeviceToHost, st));
+  LMI_CUDA(cudaStreamSynchronize(st));
+  memcpy(out_dists, idx->pin_out.p, b_d);
+  memcpy(out_ids, (char*)idx->pin_out.p + b_d, b_i);
+  return LMI_OK;
+}
+
 }  // namespace lmi
 
 extern "C" {
@@ -297,16 +339,24 @@ int lmi_search(lmi_index* idx, const float* q_nav, const uint16_t* q_f16, int64_
   LMI_CUDA(idx->ws_out_i.reserve((size_t)nq * k * 4));
   // navigation needs only the pca96 queries: the (4x larger) fp16 upload overlaps K1/K2 on a second stream.
   // (ws_q16 is free: the previous call on this index synchronised its stream before returning)
-  LMI_CUDA(cudaMemcpyAsync(idx->ws_qnav.p, q_nav, (size_t)nq * idx->d_nav * 4, cudaMemcpyHostToDevice, st));
-  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, q_f16, (size_t)nq * idx->d * 2, cudaMemcpyHostToDevice, idx->copy_stream));
+  const size_t b_nav = (size_t)nq * idx->d_nav * 4, b_q16 = (size_t)nq * idx->d * 2;
+  const void *src_nav = q_nav, *src_q16 = q_f16;
+  if (!host_ptr_is_pinned(q_nav) || !host_ptr_is_pinned(q_f16)) {       // pageable caller buffers (numpy): see parallel_memcpy
+    LMI_CUDA(idx->pin_in.reserve(b_nav + b_q16));
+    parallel_memcpy(idx->pin_in.p, q_nav, b_nav);
+    src_nav = idx->pin_in.p;
+  }
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_qnav.p, src_nav, b_nav, cudaMemcpyHostToDevice, st));
+  if (src_nav != q_nav) {                                                // (navigation is already running while the 4x larger block is gathered)
+    src_q16 = (char*)idx->pin_in.p + b_nav;
+    parallel_memcpy(const_cast<void*>(src_q16), q_f16, b_q16);
+  }
+  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, src_q16, b_q16, cudaMemcpyHostToDevice, idx->copy_stream));
   LMI_CUDA(cudaEventRecord(idx->ev_q16, idx->copy_stream));
   int rc = run_search(idx, idx->ws_qnav.as<float>(), nullptr, idx->ws_q16.as<uint16_t>(), nq, n_buckets, k, nullptr, 0,
                       idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st, idx->ev_q16);
   if (rc != LMI_OK) { cudaStreamSynchronize(idx->copy_stream); return rc; }
-  LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
-  LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-  LMI_CUDA(cudaStreamSynchronize(st));
-  return LMI_OK;
+  return copy_results_out(idx, nq, k, out_dists, out_ids, st);
 }
 
 int lmi_search_rank(lmi_index* idx, const uint16_t* q_f16, int64_t nq, const int64_t* category_per_query, int k,
@@ -331,10 +381,7 @@ int lmi_search_rank(lmi_index* idx, const uint16_t* q_f16, int64_t nq, const int
   int rc = run_search(idx, nullptr, idx->ws_cls64.as<int64_t>(), idx->ws_q16.as<uint16_t>(), nq, 1, k, thr_dev, 0,
                       idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st);
   if (rc != LMI_OK) return rc;
-  LMI_CUDA(cudaMemcpyAsync(out_dists, idx->ws_out_d.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
-  LMI_CUDA(cudaMemcpyAsync(out_ids, idx->ws_out_i.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-  LMI_CUDA(cudaStreamSynchronize(st));
-  return LMI_OK;
+  return copy_results_out(idx, nq, k, out_dists, out_ids, st);
 }
 
 int64_t lmi_partial_bytes(int64_t nq, int k) { return nq * (int64_t)k * (int64_t)sizeof(Partial); }

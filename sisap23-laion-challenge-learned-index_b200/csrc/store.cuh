@@ -143,4 +143,23 @@ store_scatter_rows_kernel(const uint16_t* __restrict__ rows, int64_t first_row, 
   }
 }
 
+// [d][n] (feature-major: how a pandas DataFrame block of [n, d] is laid out) -> [n][d] row-major, 64 x 64 tiles
+// through shared memory; both sides coalesced.  n_pitch = elements between consecutive features in `src`.
+__global__ void __launch_bounds__(256)
+store_transpose_kernel(const uint16_t* __restrict__ src, int64_t n, int d, int64_t n_pitch, uint16_t* __restrict__ dst) {
+  __shared__ uint16_t tile[64][66];
+  const int64_t r0 = (int64_t)blockIdx.x * 64;
+  const int f0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;          // 64 x 4
+  for (int f = ty; f < 64; f += 4) {
+    const int64_t r = r0 + tx;
+    tile[f][tx] = (r < n && f0 + f < d) ? src[(size_t)(f0 + f) * n_pitch + r] : (uint16_t)0;
+  }
+  __syncthreads();
+  for (int rr = ty; rr < 64; rr += 4) {
+    const int64_t r = r0 + rr;
+    if (r < n && f0 + tx < d) dst[(size_t)r * d + f0 + tx] = tile[tx][rr];
+  }
+}
+
 }  // namespace lmi

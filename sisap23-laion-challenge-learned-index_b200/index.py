@@ -18,7 +18,10 @@ the result definition.
 from __future__ import annotations
 
 import ctypes as C
+import hashlib
 import os
+import struct
+import weakref
 
 import numpy as np
 
@@ -33,18 +36,45 @@ def _ptr(a):
     return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
 
 
-def _as_rows(x):
-    """DataFrame / ndarray -> (contiguous ndarray, id_base).  The reference indexes objects by the
-    DataFrame label, which run() makes 1-based (search.py:71-72, :83-84)."""
+def _view_rows(x):
+    """DataFrame / ndarray -> (2-D ndarray VIEW, id_base) without copying the values.  The reference indexes objects by
+    the DataFrame label, which run() makes 1-based (search.py:71-72, :83-84); a 'category' column is dropped like
+    LearnedIndex.py:140-141.  A homogeneous frame hands out its block as it lies -- for a frame built from a 2-D array
+    that is an F-ordered (feature-major) view, which ``lmi_store_append_strided`` uploads without a host transpose."""
     id_base = 1
     if hasattr(x, "to_numpy") and hasattr(x, "index"):
-        cols = [c for c in x.columns if c != "category"]        # LearnedIndex.py:140-141
-        idx = np.asarray(x.index)
-        if idx.shape[0] and not np.array_equal(idx, np.arange(idx[0], idx[0] + idx.shape[0])):
-            raise ValueError("data_search index must be consecutive integers")
-        id_base = int(idx[0]) if idx.shape[0] else 1
-        x = x[cols].to_numpy() if len(cols) != x.shape[1] else x.to_numpy()
-    return np.ascontiguousarray(x), id_base
+        idx = x.index
+        n = len(idx)
+        if hasattr(idx, "start") and hasattr(idx, "step"):                  # RangeIndex: O(1)
+            if n > 1 and idx.step != 1:
+                raise ValueError("data_search index must be consecutive integers")
+            id_base = int(idx.start) if n else 1
+        elif n:
+            lab = np.asarray(idx)
+            if not np.array_equal(lab, np.arange(lab[0], lab[0] + n)):
+                raise ValueError("data_search index must be consecutive integers")
+            id_base = int(lab[0])
+        if "category" in x.columns:
+            x = x.drop(columns="category")                                  # LearnedIndex.py:140-141 (a copy, like there)
+        x = x.to_numpy()
+    return np.asarray(x), id_base
+
+
+def _as_rows(x):
+    """Same, as a C-contiguous array (small inputs: query batches, GpuBaseline)."""
+    rows, id_base = _view_rows(x)
+    return np.ascontiguousarray(rows), id_base
+
+
+def _alive(ref, obj):
+    return ref is not None and ref() is obj
+
+
+def _weak(obj):
+    try:
+        return weakref.ref(obj)
+    except TypeError:
+        return None
 
 
 def extract_mlp(model):
@@ -119,8 +149,14 @@ class GpuLearnedIndex:
         if world > 1:
             check(self._lib.lmi_set_shard(self._h, rank, world, shard_policy))
         self.rank, self.world = rank, world
+        self.shard_policy = int(shard_policy)
         self.model = None                 # like LearnedIndex.model (LearnedIndex.py:19-20)
-        self._store_key = None
+        self._store_key = None            # (content key, data address, strides) of the device store
+        self._store_refs = (None, None)   # weak references to the (data_search, pred_categories) objects it was built from
+        self._cat_sig = None              # buffer signature of the data_navigation['category'] column last seen by search_single
+        self._nav_side_effect = (None, None)
+        self.store_from_cache = False
+        self.store_builds = 0             # device stores built or loaded so far (tests assert reuse with it)
 
     # ---- lifetime ----
     def close(self):
@@ -163,23 +199,76 @@ class GpuLearnedIndex:
         return obj.set_model(w, b)
 
     # ---- store ----
-    def prepare(self, data_search, pred_categories):
-        """Build (or reuse) the device bucket store for (data_search, pred_categories).  The
-        reference regroups and regathers on every rank of every search (LearnedIndex.py:143,152);
-        here it happens once per dataset and is keyed on the inputs' identity."""
-        rows, id_base = _as_rows(data_search)
-        pc = np.ascontiguousarray(np.asarray(pred_categories, dtype=np.int64))
-        key = (id(data_search), rows.shape, int(pc.shape[0]), int(pc[:: max(1, pc.shape[0] // 997)].sum()))
-        if key == self._store_key:
+    def _content_key(self, rows, id_base, pc):
+        """32-byte fingerprint of what the device store is a function of: ALL of pred_categories (8 bytes x N is
+        cheap next to the upload), the shapes, id_base, the shard, and 66 sampled rows of the data.  Names the
+        on-disk cache file and is stored inside it."""
+        h = hashlib.blake2b(digest_size=32)
+        h.update(memoryview(pc).cast("B"))
+        n = rows.shape[0]
+        h.update(struct.pack("<qqqiii", n, rows.shape[1], id_base, self.rank, self.world, self.shard_policy))
+        h.update(str(rows.dtype).encode())
+        if n:
+            pick = np.unique(np.concatenate([np.arange(0, n, max(1, n // 64)), [n - 1]]))
+            h.update(np.ascontiguousarray(rows[pick]).tobytes())
+        return h.digest()
+
+    def invalidate(self):
+        """Forget the cached store: the next prepare()/search() rebuilds it (call after editing the arrays in place)."""
+        self._store_key = None
+        self._store_refs = (None, None)
+        self._cat_sig = None
+
+    def prepare(self, data_search, pred_categories, force=False, cache_dir=None):
+        """Build (or reuse) the device bucket store for (data_search, pred_categories).  The reference regroups and
+        regathers on every rank of every search (LearnedIndex.py:143,152); here it happens once per dataset.
+
+        Reuse rules (nothing below converts or copies ``data_search``): (1) the very same live objects as last time ->
+        reused at once; (2) otherwise a full hash of ``pred_categories`` plus the data's buffer address, layout and 66
+        sampled rows are compared with the store's -> reused if equal (e.g. ``df.values`` temporaries); (3) else
+        rebuilt.  In-place edits of the same objects are not seen: pass ``force=True`` or call ``invalidate()``.
+        ``cache_dir``: keep / look up the finished device layout on disk (``lmi_store_save`` / ``lmi_store_load``),
+        file name = the content key."""
+        if not force and self._store_key is not None and _alive(self._store_refs[0], data_search) and \
+                _alive(self._store_refs[1], pred_categories):
             return self
-        if rows.dtype != np.float16:
-            rows = rows.astype(np.float16)            # clip768v2 'emb' is float16 (search.py:79-81)
+        pc = np.ascontiguousarray(np.asarray(pred_categories, dtype=np.int64))
+        rows, id_base = _view_rows(data_search)
         if rows.ndim != 2 or rows.shape[1] != self.d:
             raise ValueError(f"data_search must be [N, {self.d}]")
         if pc.shape[0] != rows.shape[0]:
             raise ValueError("pred_categories length != number of objects")
-        check(self._lib.lmi_set_buckets(self._h, _ptr(rows.view(np.uint16)), _ptr(pc), rows.shape[0], id_base))
+        ckey = self._content_key(rows, id_base, pc)
+        key = (ckey, rows.__array_interface__["data"][0], rows.strides)
+        if not force and key == self._store_key:
+            self._store_refs = (_weak(data_search), _weak(pred_categories))
+            return self
+        if rows.dtype != np.float16:
+            rows = rows.astype(np.float16)            # clip768v2 'emb' is float16 (search.py:79-81)
+        es = rows.dtype.itemsize
+        if not ((rows.strides[1] == es and rows.strides[0] >= self.d * es and rows.strides[0] % es == 0) or
+                (rows.strides[0] == es and rows.strides[1] >= rows.shape[0] * es and rows.strides[1] % es == 0)):
+            rows = np.ascontiguousarray(rows)         # exotic strides only; frames and arrays never get here
+        path = None
+        if cache_dir is not None:
+            os.makedirs(cache_dir, exist_ok=True)
+            path = os.path.join(cache_dir, f"lmi_store_{ckey.hex()[:32]}.bin")
+        loaded = False
+        if path is not None and os.path.exists(path):
+            loaded = self._lib.lmi_store_load(self._h, path.encode(), ckey) == 0     # any mismatch -> rebuild below
+        if not loaded:
+            n = rows.shape[0]
+            check(self._lib.lmi_store_begin(self._h, _ptr(pc), n, id_base, 0))
+            check(self._lib.lmi_store_append_strided(self._h, C.c_void_p(rows.ctypes.data), 0, n,
+                                                     rows.strides[0] // es, rows.strides[1] // es, 0))
+            check(self._lib.lmi_store_end(self._h))
+            if path is not None:
+                check(self._lib.lmi_store_save(self._h, path.encode(), ckey))
+        self.store_from_cache = loaded
+        self.store_builds += 1
         self._store_key = key
+        self._store_refs = (_weak(data_search), _weak(pred_categories))
+        self._cat_sig = None
         return self
 
     def prepare_device(self, data_f16_t, pred_categories_t, id_base=1, chunk_rows=1 << 20):
@@ -193,6 +282,8 @@ class GpuLearnedIndex:
             check(self._lib.lmi_store_append(self._h, C.c_void_p(data_f16_t[lo:lo + cnt].data_ptr()), lo, cnt, 1))
         check(self._lib.lmi_store_end(self._h))
         self._store_key = ("device", n)
+        self._store_refs = (None, None)
+        self._cat_sig = None
         return self
 
     def bucket_ptr(self):
@@ -205,8 +296,18 @@ class GpuLearnedIndex:
                n_buckets=1, k=10, use_threshold=False):
         assert self.model is not None, 'Model is not trained, call `build` first.'      # LearnedIndex.py:60
         if data_navigation is not None and hasattr(data_navigation, "columns"):
-            data_navigation['category'] = pred_categories                                # LearnedIndex.py:67
+            # LearnedIndex.py:67 mutates the caller's frame on every call (an 80 MB column copy at 10M); skipped when
+            # the same live frame already received the same live pred_categories object from the previous call
+            same = _alive(self._nav_side_effect[0], data_navigation) and _alive(self._nav_side_effect[1], pred_categories) \
+                and "category" in data_navigation.columns
+            if not same:
+                data_navigation['category'] = pred_categories
+                self._nav_side_effect = (_weak(data_navigation), _weak(pred_categories))
         self.prepare(data_search, pred_categories)
+        return self._search_prepared(queries_navigation, queries_search, n_buckets, k)
+
+    def _search_prepared(self, queries_navigation, queries_search, n_buckets, k):
+        """The search proper on the store prepared last (host buffers in and out through ``lmi_search``)."""
         qn = np.ascontiguousarray(np.asarray(queries_navigation, dtype=np.float32))      # model.py:88
         qs = np.ascontiguousarray(np.asarray(queries_search, dtype=np.float16))
         nq = qs.shape[0]
@@ -223,12 +324,22 @@ class GpuLearnedIndex:
     def search_single(self, data_navigation, data_search, queries_search, pred_categories, k=10,
                       threshold_dist=None):
         """``pred_categories`` here is the category of every *query* at one rank (as in the reference).
-        The object->bucket assignment comes from ``data_navigation['category']`` (LearnedIndex.py:143)
-        unless a store was prepared already."""
-        if self._store_key is None:
-            if data_navigation is None or "category" not in getattr(data_navigation, "columns", []):
+        The object->bucket assignment is ``data_navigation['category']`` (the reference regroups by it on every call,
+        LearnedIndex.py:143): the store is reused when that column is the one it was built from (same frame, same
+        column buffer; else its full hash is compared) and rebuilt when it changed.  Without the column (``None``
+        frame) a store prepared earlier is used."""
+        cat_col = None
+        if data_navigation is not None and "category" in getattr(data_navigation, "columns", []):
+            cat_col = data_navigation["category"].to_numpy()
+        if cat_col is None:
+            if self._store_key is None:
                 raise AssertionError("no bucket store: call prepare() or pass data_navigation with a 'category' column")
-            self.prepare(data_search, np.asarray(data_navigation["category"]))
+        else:
+            sig = (cat_col.__array_interface__["data"][0], cat_col.shape, cat_col.strides, str(cat_col.dtype))
+            if not (self._store_key is not None and sig == self._cat_sig and _alive(self._store_refs[0], data_search)):
+                self._store_refs = (None, None)                 # force the content comparison (full hash of the column)
+                self.prepare(data_search, cat_col)
+                self._cat_sig = sig
         qs = np.ascontiguousarray(np.asarray(queries_search, dtype=np.float16))
         nq = qs.shape[0]
         cat = np.ascontiguousarray(np.asarray(pred_categories, dtype=np.int64))
@@ -294,7 +405,7 @@ class GpuBaseline:
         import time
         s = time.time()
         rows, _ = _as_rows(data)
-        key = (id(data), rows.shape)
+        key = (rows.shape, hashlib.blake2b(rows.tobytes(), digest_size=16).digest())     # (documented for < 1M objects, Baseline.py:8-10)
         if key != self._key:
             if self._li is not None:
                 self._li.close()

@@ -110,6 +110,38 @@ def test_search_single_matches_reference(tag, rescore):
     assert (at[~keep] == 0).all() and (dt[~keep] == 10000.0).all()
 
 
+@pytest.mark.parametrize("rescore", [0, 1, 3], ids=["simt", "tcgen05-tmemA", "tcgen05-pair"])
+@pytest.mark.parametrize("tag", GOLDEN_TAGS)
+def test_search_single_threshold_matches_reference_and_oracle(tag, rescore):
+    """Row a7 (utils.py:14-43 through LearnedIndex.py:149-163): ``lmi_search_rank(threshold)`` against (a) the oracle's
+    intended semantics with the same thresholds -- every slot, pruned slots are (0, 10000.0) on both sides -- and
+    (b) the arrays the reference's own ``search_single(threshold_dist=...)`` returned (tests/golden, made by
+    oracle/make_golden.py), on the live slots (dist < 10000; the reference pads the others with arbitrary ids)
+    of the rows its '<k' defect did not touch."""
+    from oracle import lmi_oracle as O
+    g = load_golden(tag)
+    li = _index(g, rescore)
+    li.prepare(g["data_f16"], g["pred_categories"])
+    k = g["k"]
+    for key, rank in (("single_thr", 1), ("single_thr2", 0)):
+        thr, ref_d, ref_a, d1 = g[key], g[key + "_dists"], g[key + "_ids"], g[key + "_d1"]
+        cats = g["classes"][:, rank]
+        d, a = li.search_single(None, g["data_f16"], g["queries_f16"], cats, k=k, threshold_dist=thr)
+        od, oa = O.search_intended(cats[:, None], g["data_f16"], g["queries_f16"], g["pred_categories"], 1, k, thresholds=thr)
+        assert_ids_equal_up_to_ties(a, d, oa, od, what=f"{tag} {key} vs oracle")
+        _check_dists(d, od)
+        assert ((d < 10000.0) == (od < 10000.0)).all()
+        assert (a[d == 10000.0] == 0).all()
+        assert (d[d < 10000.0] < np.repeat(thr[:, None], k, 1)[d < 10000.0]).all()          # strict '<' (utils.py:23)
+        ok = ~d1
+        live = ref_d[ok] < 10000.0
+        assert ((d[ok] < 10000.0) == live).all(), f"{tag} {key}: survivors per row differ from the reference"
+        assert_ids_equal_up_to_ties(np.where(live, a[ok], 0), d[ok], np.where(live, ref_a[ok], 0), ref_d[ok],
+                                    what=f"{tag} {key} vs reference")
+        _check_dists(d[ok], ref_d[ok])
+        assert li.stats()["n_uncertified"] == 0
+
+
 def test_exhaustive_equals_reference_baseline():
     """n_buckets = C probes every bucket: must equal the reference's brute force (Baseline.py:14-20)."""
     g = load_golden("ref_mlp5_n1600_c16")

@@ -67,6 +67,31 @@ def test_seeded_vs_oracle(case, nb, k):
     assert (a2 == a).all() and (d2 == d).all()                              # idempotent / deterministic
 
 
+@pytest.mark.parametrize("k", [10, 50])
+def test_search_rank_threshold_vs_oracle(case, k):
+    """lmi_search_rank with per-query thresholds (the reference's search_single(threshold_dist=...),
+    LearnedIndex.py:149-163 / utils.py:22-23) against the oracle's thresholded semantics at 40k objects:
+    the running threshold search() would use for rank 1, and a per-query random quantile of rank 0's distances."""
+    from oracle import lmi_oracle as O
+    c = case
+    li = _index(c)                                  # library default kernel
+    d0, a0 = li.search_single(None, c["data_f16"], c["queries_f16"], c["classes"][:, 0], k=k)
+    rng = np.random.default_rng(5)
+    for cats, thr in ((c["classes"][:, 1], d0.max(axis=1)),
+                      (c["classes"][:, 0], d0[np.arange(d0.shape[0]), rng.integers(0, k, d0.shape[0])])):
+        d, a = li.search_single(None, c["data_f16"], c["queries_f16"], cats, k=k, threshold_dist=thr)
+        od, oa = O.search_intended(cats[:, None], c["data_f16"], c["queries_f16"], c["pred_categories"], 1, k, thresholds=thr)
+        # a distance that equals its threshold to the last bit may fall on either side of the strict '<'
+        # (float64 summation order): such rows are excluded, there must be next to none
+        edge = (np.abs(od - thr[:, None]) < 1e-12).any(axis=1) | (np.abs(d - thr[:, None]) < 1e-12).any(axis=1)
+        assert edge.mean() < 0.02
+        ok = ~edge
+        assert_ids_equal_up_to_ties(a[ok], d[ok], oa[ok], od[ok], what=f"search_rank threshold k={k}")
+        np.testing.assert_allclose(d[ok], od[ok], rtol=1e-3, atol=1e-9)
+        assert (a[d == 10000.0] == 0).all()
+        assert li.stats()["n_uncertified"] == 0
+
+
 @pytest.mark.parametrize("nb,k", [(4, 10), (3, 50), (2, 100)])
 def test_tc_equals_simt(case, nb, k):
     c = case

@@ -83,3 +83,36 @@ def test_brute_force_and_recall(golden):
     nb = g["bucket_list"][-1]
     r = O.get_recall(g[f"clean_ids_nb{nb}"][:sub], g["baseline_ids"], g["k"])
     assert 0.0 < r <= 1.0
+
+
+def _live(dists):
+    return dists < O.EMPTY_DIST
+
+
+def test_search_single_threshold_path(golden):
+    """Row a7: ``search_single(threshold_dist=...)`` -> ``pairwise_cosine_threshold`` (LearnedIndex.py:149-163,
+    utils.py:14-43) as ``search()`` drives it for rank 1, and with a tighter threshold on rank 0's categories.
+    The faithful loops reproduce the reference's arrays (D1 rows included: same padding code); the intended
+    semantics agree with it on every live slot (dist < 10000) of the rows D1 did not touch."""
+    g = golden
+    table = O.BucketTable(g["pred_categories"], 1)
+    for key, rank in (("single_thr", 1), ("single_thr2", 0)):
+        thr, ref_d, ref_a, d1 = g[key], g[key + "_dists"], g[key + "_ids"], g[key + "_d1"]
+        cats = g["classes"][:, rank]
+        flagged = np.zeros(thr.shape[0], dtype=bool)
+        d, a = O.search_single_loops(table, g["data_f16"], g["queries_f16"], cats, g["k"], thr, flagged=flagged)
+        assert (flagged == d1).all()                                  # same rows go through the '<k' branch
+        np.testing.assert_allclose(d, ref_d, rtol=0, atol=1e-12)
+        live = _live(ref_d)
+        assert (a[live & ~d1[:, None]] == ref_a[live & ~d1[:, None]]).mean() > 0.999      # (ties aside)
+        # strict '<' (utils.py:23): nothing at or above the threshold survives on an unflagged row
+        assert (ref_d[~d1][_live(ref_d[~d1])] < np.repeat(thr[~d1, None], g["k"], 1)[_live(ref_d[~d1])]).all()
+        # intended semantics with thresholds: identical on live slots of unflagged rows
+        classes1 = cats[:, None]
+        od, oa = O.search_intended(classes1, g["data_f16"], g["queries_f16"], g["pred_categories"], 1, g["k"],
+                                   thresholds=thr)
+        ok = ~d1
+        assert (_live(od[ok]) == _live(ref_d[ok])).all()              # same number of survivors per row
+        assert_ids_equal_up_to_ties(np.where(_live(od[ok]), oa[ok], 0), od[ok],
+                                    np.where(_live(ref_d[ok]), ref_a[ok], 0), ref_d[ok], what=key)
+        np.testing.assert_allclose(od[ok], ref_d[ok], rtol=0, atol=1e-12)
