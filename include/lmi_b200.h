@@ -59,7 +59,8 @@ typedef struct {
   int64_t pairs;                 /* sum_b m_b * n_b  (query-object pairs scored, no padding) */
   int64_t bucket_bytes;          /* 2*d*sum_{b: m_b>0} n_b  (fp16 bytes of every probed bucket, once) */
   int64_t n_partial_lists;       /* partial top-k' lists written by the rescoring kernel */
-  int64_t n_uncertified;         /* queries whose exactness certificate failed */
+  int64_t n_uncertified;         /* queries whose exactness certificate failed and that were therefore re-derived exactly
+                                    (float64 over every probed object) by the fallback kernel */
   double  max_abs_score_err;     /* max |fp32 cosine - fp64 cosine| over refined candidates */
   /* device time of the last search, milliseconds (CUDA events on the search stream) */
   float ms_navigate, ms_plan, ms_rescore, ms_finalize, ms_total;

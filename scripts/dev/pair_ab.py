@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 
 
-def diag(nq=256):
+def diag(nq=256, sets=0):
     import torch
     from lmi_b200.index import GpuLearnedIndex
     rng = np.random.default_rng(7)
@@ -35,6 +35,7 @@ def diag(nq=256):
     res = {}
     for name, r in (("ts", 1), ("ts2", 3)):
         li = GpuLearnedIndex(1, d=d, rescore=r, chunk_objects=2048)
+        li.set_option("epi_sets", sets)
         li.prepare(x16, pc)
         dd, aa = li.search_single(None, x16, q16, cat, k=10)
         st = li.stats()
@@ -70,6 +71,7 @@ def main():
     ap.add_argument("--seq", default="", help="explicit run sequence 'rescore:chunk:flags,...' (replaces the default A/B order; "
                                               "interleave variants -- the power-capped clock drifts over a process lifetime)")
     ap.add_argument("--dbg-pair-only", action="store_true", help="run the --dbg flags on the pair kernel only")
+    ap.add_argument("--diag-sets", type=int, default=0, help="epi_sets used by the diagnosis stage (0 = automatic)")
     ap.add_argument("--exp", action="store_true", help="load liblmi_b200_exp.so (-DLMI_EXPERIMENTS build: dbg_flags honoured)")
     a = ap.parse_args()
     if a.exp:
@@ -79,10 +81,10 @@ def main():
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     report = {}
     if not a.skip_diag:
-        report["diag"] = diag(256)
+        report["diag"] = diag(256, a.diag_sets)
         print(json.dumps(report["diag"]), flush=True)
         json.dump(report, open(a.out, "w"), indent=1)
-        report["diag_odd_tile"] = diag(300)          # 3 query tiles: a full pair + a split odd tile
+        report["diag_odd_tile"] = diag(300, a.diag_sets)          # 3 query tiles: a full pair + a split odd tile
         print(json.dumps(report["diag_odd_tile"]), flush=True)
         json.dump(report, open(a.out, "w"), indent=1)
         if a.diag_only or report["diag"]["rows_mismatch"] or report["diag_odd_tile"]["rows_mismatch"]:

@@ -31,6 +31,63 @@ __device__ __forceinline__ bool key_less(double da, uint32_t ra, uint32_t ia, in
   return ga < gb;
 }
 
+// float64 dot(q, x) and |x|^2 of one candidate row by a group of 8 lanes (sub = lane & 7): lane `sub` takes the
+// 16-byte vectors sub, sub + 8, ... in ascending order, then the 8 partial sums are folded with xor-shuffles 4, 2, 1.
+// The operation sequence is spelled out with intrinsics so that every caller (K5 and the exact fallback) produces
+// bit-identical distances for the same (query, object) pair -- which keeps results independent of the path taken
+// and of the number of GPUs.  sq: the query row in shared memory; returns the reduced sums in every lane of the group.
+__device__ __forceinline__ void fin_dot_group(const uint4* __restrict__ xrow, const uint4* sq, int vec, int sub,
+                                              double& dot_out, double& xx_out) {
+  constexpr int kUn = 6;                       // 6 x 16 bytes per lane in flight (the rows are random 1.5 KB HBM reads)
+  double dot = 0.0, xx = 0.0;
+  for (int v0 = sub; v0 < vec; v0 += 8 * kUn) {
+    uint4 ux[kUn];
+#pragma unroll
+    for (int u = 0; u < kUn; ++u) { const int v = v0 + 8 * u; ux[u] = (v < vec) ? __ldg(xrow + v) : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+    for (int u = 0; u < kUn; ++u) {
+      const int v = v0 + 8 * u;
+      if (v < vec) {
+        const uint4 uq = sq[v];
+        const __half2* hx = reinterpret_cast<const __half2*>(&ux[u]);
+        const __half2* hq = reinterpret_cast<const __half2*>(&uq);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 fx = __half22float2(hx[j]);
+          const float2 fq = __half22float2(hq[j]);
+          const double ax = (double)fx.x, ay = (double)fx.y;
+          dot = __dadd_rn(dot, __fma_rn(ay, (double)fq.y, __dmul_rn(ax, (double)fq.x)));
+          xx = __dadd_rn(xx, __fma_rn(ay, ay, __dmul_rn(ax, ax)));
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {                     // sum over the 8 lanes of the group
+    dot = __dadd_rn(dot, __shfl_xor_sync(0xffffffffu, dot, o));
+    xx = __dadd_rn(xx, __shfl_xor_sync(0xffffffffu, xx, o));
+  }
+  dot_out = dot; xx_out = xx;
+}
+
+// |q| in float64 by one warp (lane takes vectors lane, lane + 32, ...; xor-shuffle fold 16..1) and the row into shared memory
+__device__ __forceinline__ double fin_load_query(const uint4* __restrict__ qrow, uint4* sq, int vec, int lane) {
+  double qq = 0.0;
+  for (int v = lane; v < vec; v += 32) {
+    const uint4 u = qrow[v];
+    sq[v] = u;
+    const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __half22float2(h[j]);
+      const double ax = (double)f.x, ay = (double)f.y;
+      qq = __dadd_rn(qq, __fma_rn(ay, ay, __dmul_rn(ax, ax)));
+    }
+  }
+  qq = warp_sum(qq);
+  return (qq == 0.0) ? 1.0 : sqrt(qq);
+}
+
 // mode 0: write out_dists/out_ids [nq,k];  mode 1: write Partial [nq,k]
 __global__ void __launch_bounds__(kFinWarps * 32)
 finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
@@ -39,7 +96,7 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
                 const int64_t* __restrict__ plist_base, const Cand* __restrict__ plists,
                 const uint16_t* __restrict__ q, const uint16_t* __restrict__ store,
                 const uint32_t* __restrict__ ids, const double* __restrict__ threshold,
-                PlanScalars* __restrict__ sc, int mode,
+                PlanScalars* __restrict__ sc, int32_t* __restrict__ uncert_list, int mode,
                 double* __restrict__ out_dists, uint32_t* __restrict__ out_ids,
                 Partial* __restrict__ out_partial) {
   __shared__ int32_t s_pos[kFinWarps][kMaxKPrime];
@@ -190,53 +247,18 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   const int vec = d / 8;                                  // uint4 per row (d is a multiple of 64)
   const uint4* qrow = reinterpret_cast<const uint4*>(q + (size_t)qi * d);
   uint4* sq = s_q[warp];
-  double qq = 0.0;
-  for (int v = lane; v < vec; v += 32) {
-    const uint4 u = qrow[v];
-    sq[v] = u;
-    const __half2* h = reinterpret_cast<const __half2*>(&u);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { const float2 f = __half22float2(h[j]); qq += (double)f.x * f.x + (double)f.y * f.y; }
-  }
-  qq = warp_sum(qq);
-  const double qn = (qq == 0.0) ? 1.0 : sqrt(qq);
+  const double qn = fin_load_query(qrow, sq, vec, lane);
   double max_err = 0.0;
   const float score_R = (n_sel == R) ? (float)s_dist[warp][R - 1] : 0.f;     // before the scores are overwritten
   __syncwarp();
   const int grp = lane >> 3, sub = lane & 7;
-  constexpr int kUn = 6;
   for (int t0 = 0; t0 < n_sel; t0 += 4) {
     const int t = t0 + grp;
     const bool valid = t < n_sel;
     const int32_t pos = s_pos[warp][valid ? t : t0];
     const uint4* xrow = reinterpret_cast<const uint4*>(store + (size_t)pos * d);
-    double dot = 0.0, xx = 0.0;
-    for (int v0 = sub; v0 < vec; v0 += 8 * kUn) {
-      uint4 ux[kUn];
-#pragma unroll
-      for (int u = 0; u < kUn; ++u) { const int v = v0 + 8 * u; ux[u] = (v < vec) ? __ldg(xrow + v) : make_uint4(0, 0, 0, 0); }
-#pragma unroll
-      for (int u = 0; u < kUn; ++u) {
-        const int v = v0 + 8 * u;
-        if (v < vec) {
-          const uint4 uq = sq[v];
-          const __half2* hx = reinterpret_cast<const __half2*>(&ux[u]);
-          const __half2* hq = reinterpret_cast<const __half2*>(&uq);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 fx = __half22float2(hx[j]);
-            const float2 fq = __half22float2(hq[j]);
-            dot += (double)fx.x * (double)fq.x + (double)fx.y * (double)fq.y;
-            xx += (double)fx.x * (double)fx.x + (double)fx.y * (double)fx.y;
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int o = 4; o > 0; o >>= 1) {                     // sum over the 8 lanes of the group
-      dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      xx += __shfl_xor_sync(0xffffffffu, xx, o);
-    }
+    double dot, xx;
+    fin_dot_group(xrow, sq, vec, sub, dot, xx);
     if (valid && sub == 0) {
       const double xn = (xx == 0.0) ? 1.0 : sqrt(xx);
       const double cos64 = dot / (qn * xn);
@@ -287,11 +309,118 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
     if (n_sel == R) {
       const double cos_dropped = (double)score_R / qn + kCertEps;
       const double cos_kth = 1.0 - kth_dist;     // kth_dist = 10000 if fewer than k results -> uncertified
-      if (!(cos_dropped < cos_kth)) atomicAdd(&sc->n_uncertified, 1ull);
+      if (!(cos_dropped < cos_kth)) {
+        // not provably exact: listed for exact_fixup_kernel, which re-derives the row from every probed object
+        const unsigned long long u = atomicAdd(&sc->n_uncertified, 1ull);
+        uncert_list[u] = (int32_t)qi;                 // capacity nq: every query is listed at most once
+      }
     }
     // 10k same-address atomics serialise in L2 (~0.15 ms per search): only a new maximum goes there
     const unsigned long long bits = (unsigned long long)__double_as_longlong(max_err);
     if (bits > __ldcg(&sc->max_err_bits)) atomicMax(&sc->max_err_bits, bits);
+  }
+}
+
+// Exactness fallback.  K3 selects by fp32 scores and K5 certifies, per query, that nothing it dropped can belong to the
+// float64 top-k; a query whose certificate fails (near-ties denser than k' - k at the k-th place, or fp32 error above the
+// bound) is re-derived here from EVERY object of its probed buckets in float64 -- the reference's own arithmetic
+// (utils.py:10-11) over the reference's own candidate set (LearnedIndex.py:143-172) -- so "ids bit-exact" does not rest
+// on the certificate's error bound.  Launched after every finalize; exits at once when nothing is listed (the usual
+// case).  One CTA per listed query, a group of 8 lanes per object (same arithmetic as K5: fin_dot_group), per-warp
+// k-best lists in shared memory, merged by rank counting.
+constexpr int kFixWarps = 8;
+__global__ void __launch_bounds__(kFixWarps * 32)
+exact_fixup_kernel(int64_t nq, int nb, int k, int d, const int32_t* __restrict__ top_cls,
+                   const int32_t* __restrict__ pair_slot, const int64_t* __restrict__ bucket_ptr,
+                   const uint16_t* __restrict__ q, const uint16_t* __restrict__ store, const uint32_t* __restrict__ ids,
+                   const double* __restrict__ threshold, const PlanScalars* __restrict__ sc,
+                   const int32_t* __restrict__ uncert_list, int mode,
+                   double* __restrict__ out_dists, uint32_t* __restrict__ out_ids, Partial* __restrict__ out_partial) {
+  __shared__ double s_d[kFixWarps][kMaxKPrime];
+  __shared__ uint32_t s_r[kFixWarps][kMaxKPrime];
+  __shared__ uint32_t s_i[kFixWarps][kMaxKPrime];
+  __shared__ int s_cnt[kFixWarps];
+  __shared__ uint4 s_q[kFinMaxVec];
+  __shared__ double s_qn;
+  const int n_list = (int)min((unsigned long long)nq, sc->n_uncertified);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int grp = lane >> 3, sub = lane & 7;
+  const int vec = d / 8;
+  for (int u = blockIdx.x; u < n_list; u += gridDim.x) {
+    const int64_t qi = uncert_list[u];
+    __syncthreads();                                       // previous query's shared state is no longer read
+    if (warp == 0) {
+      const double qn = fin_load_query(reinterpret_cast<const uint4*>(q + (size_t)qi * d), s_q, vec, lane);
+      if (lane == 0) s_qn = qn;
+    }
+    __syncthreads();
+    const double qn = s_qn;
+    int cnt = 0;                                           // entries in this warp's list (warp-uniform)
+    int worst = 0;                                         // entry holding the largest key once the list is full
+    for (int r = 0; r < nb; ++r) {
+      const int64_t e = qi * nb + r;
+      if (pair_slot[e] < 0) continue;                      // empty / out-of-range category: contributes nothing
+      const int b = top_cls[e];
+      const int64_t o0 = bucket_ptr[b], o1 = bucket_ptr[b + 1];
+      for (int64_t base = o0 + (int64_t)warp * 4; base < o1; base += kFixWarps * 4) {
+        const int64_t pos = base + grp;
+        const bool valid = pos < o1;
+        double dot, xx;
+        fin_dot_group(reinterpret_cast<const uint4*>(store + (size_t)(valid ? pos : o0) * d), s_q, vec, sub, dot, xx);
+        const double xn = (xx == 0.0) ? 1.0 : sqrt(xx);
+        const double dist = 1.0 - dot / (qn * xn);
+        const uint32_t id = valid ? ids[pos] : 0u;
+        for (int g4 = 0; g4 < 4; ++g4) {                   // the warp inserts its (up to) 4 candidates one after the other
+          if (!__shfl_sync(0xffffffffu, (int)valid, g4 * 8)) continue;
+          const double cd = __shfl_sync(0xffffffffu, dist, g4 * 8);
+          const uint32_t ci = __shfl_sync(0xffffffffu, id, g4 * 8);
+          int slot = -1;
+          if (cnt < k) slot = cnt++;
+          else if (key_less(cd, (uint32_t)r, ci, 0, s_d[warp][worst], s_r[warp][worst], s_i[warp][worst], 0)) slot = worst;
+          if (slot < 0) continue;                          // warp-uniform
+          __syncwarp();
+          if (lane == 0) { s_d[warp][slot] = cd; s_r[warp][slot] = (uint32_t)r; s_i[warp][slot] = ci; }
+          __syncwarp();
+          if (cnt == k) {                                  // (re)locate the largest key of the full list
+            double wd = -1.0; uint32_t wr = 0, wi = 0; int wj = -1;
+            for (int j = lane; j < k; j += 32)
+              if (wj < 0 || key_less(wd, wr, wi, 0, s_d[warp][j], s_r[warp][j], s_i[warp][j], 0)) { wd = s_d[warp][j]; wr = s_r[warp][j]; wi = s_i[warp][j]; wj = j; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              const double od = __shfl_xor_sync(0xffffffffu, wd, o);
+              const uint32_t orr = __shfl_xor_sync(0xffffffffu, wr, o), oi = __shfl_xor_sync(0xffffffffu, wi, o);
+              const int oj = __shfl_xor_sync(0xffffffffu, wj, o);
+              if (oj >= 0 && (wj < 0 || key_less(wd, wr, wi, 0, od, orr, oi, 0))) { wd = od; wr = orr; wi = oi; wj = oj; }
+            }
+            worst = wj;
+          }
+        }
+      }
+    }
+    if (lane == 0) s_cnt[warp] = cnt;
+    __syncthreads();
+    // ---- merge the warps' lists: the position of an entry = number of entries with a smaller key ----
+    const double thr = threshold ? threshold[qi] : 1.0e300;
+    int total = 0;
+    for (int w = 0; w < kFixWarps; ++w) total += s_cnt[w];
+    for (int t = threadIdx.x; t < kFixWarps * k; t += blockDim.x) {
+      const int w = t / k, j = t - w * k;
+      if (j >= s_cnt[w]) continue;
+      const double dt = s_d[w][j]; const uint32_t rt = s_r[w][j], it = s_i[w][j];
+      int ord = 0;
+      for (int w2 = 0; w2 < kFixWarps; ++w2)
+        for (int j2 = 0; j2 < s_cnt[w2]; ++j2)
+          ord += key_less(s_d[w2][j2], s_r[w2][j2], s_i[w2][j2], w2 * k + j2, dt, rt, it, t) ? 1 : 0;
+      if (ord < k) {
+        const bool keep = dt < thr;
+        if (mode == 0) { out_dists[qi * k + ord] = keep ? dt : kEmptyDist; out_ids[qi * k + ord] = keep ? it : 0u; }
+        else { Partial p; p.dist = keep ? dt : kEmptyDist; p.id = keep ? it : 0u; p.rank = keep ? rt : 0xffffffffu; out_partial[qi * k + ord] = p; }
+      }
+    }
+    for (int o = total + threadIdx.x; o < k; o += blockDim.x) {
+      if (mode == 0) { out_dists[qi * k + o] = kEmptyDist; out_ids[qi * k + o] = 0u; }
+      else { Partial p; p.dist = kEmptyDist; p.id = 0u; p.rank = 0xffffffffu; out_partial[qi * k + o] = p; }
+    }
   }
 }
 

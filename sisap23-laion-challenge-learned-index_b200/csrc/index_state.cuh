@@ -109,7 +109,7 @@ struct lmi_index {
   // search workspace (grow-only)
   lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;
   lmi::PinBuf pin_in, pin_out;               // staging for pageable caller buffers (lmi_search / lmi_search_rank)
-  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr;
+  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr, uncert;
   lmi::DevBuf nav_cls, nav_probs, nav_x;
   CUtensorMap tmap_q{};
   void* tmap_q_ptr = nullptr; size_t tmap_q_rows = 0;

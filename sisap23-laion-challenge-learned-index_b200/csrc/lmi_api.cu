@@ -117,7 +117,7 @@ void lmi_destroy(lmi_index* idx) {
                     &idx->owner, &idx->bucket_ptr, &idx->stage_rows, &idx->ws_qnav, &idx->ws_q16, &idx->ws_out_d,
                     &idx->ws_out_i, &idx->ws_thr, &idx->ws_cls64, &idx->top_cls, &idx->m_b, &idx->qoff,
                     &idx->chunks_b, &idx->plist_base, &idx->slot_pair, &idx->pair_slot, &idx->items, &idx->plists,
-                    &idx->qg, &idx->scalars, &idx->qthr, &idx->nav_cls, &idx->nav_probs, &idx->nav_x, &idx->stage_rows_t};
+                    &idx->qg, &idx->scalars, &idx->qthr, &idx->nav_cls, &idx->nav_probs, &idx->nav_x, &idx->stage_rows_t, &idx->uncert};
   for (DevBuf* b : bufs) b->release();
   if (idx->x) cudaFree(idx->x);
   if (idx->inv_norm) cudaFree(idx->inv_norm);

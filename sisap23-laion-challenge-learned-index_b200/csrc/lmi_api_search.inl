@@ -166,6 +166,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   LMI_CUDA(idx->slot_pair.reserve((size_t)n_pairs * 4));
   LMI_CUDA(idx->pair_slot.reserve((size_t)n_pairs * 4));
   LMI_CUDA(idx->scalars.reserve(sizeof(PlanScalars)));
+  LMI_CUDA(idx->uncert.reserve((size_t)nq * 4));
   const int64_t qtiles_max = (nq + kTileQ - 1) / kTileQ;
   const int chunk = choose_chunk(idx, nq, nb, KP);
   idx->chunk_now = chunk;
@@ -253,7 +254,12 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   finalize_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, st>>>(
       nq, nb, k, KP, d, top, idx->pair_slot.as<int32_t>(), idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(),
       idx->plist_base.as<int64_t>(), idx->plists.as<Cand>(), q16_dev, idx->x, idx->ids, thr_dev,
-      idx->scalars.as<PlanScalars>(), mode, out_d, out_i, out_p);
+      idx->scalars.as<PlanScalars>(), idx->uncert.as<int32_t>(), mode, out_d, out_i, out_p);
+  // exactness fallback: queries whose certificate failed are re-derived in float64 from every probed object
+  // (exits at once when the list is empty, which is the usual case)
+  exact_fixup_kernel<<<idx->num_sms, kFixWarps * 32, 0, st>>>(
+      nq, nb, k, d, top, idx->pair_slot.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), q16_dev, idx->x, idx->ids, thr_dev,
+      idx->scalars.as<PlanScalars>(), idx->uncert.as<int32_t>(), mode, out_d, out_i, out_p);
   LMI_CUDA(cudaGetLastError());
   if (timing) LMI_CUDA(cudaEventRecord(idx->ev[4], st));
   LMI_CUDA(cudaMemcpyAsync(idx->h_scalars, idx->scalars.p, sizeof(PlanScalars), cudaMemcpyDeviceToHost, st));

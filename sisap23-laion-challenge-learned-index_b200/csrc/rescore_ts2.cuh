@@ -50,7 +50,13 @@ namespace lmi {
 constexpr int kT2HalfN = kTsBlockN / 2;                            // objects per CTA and tile
 constexpr int kT2AtomBytes = kT2HalfN * kTsAtomK * 2;              // 4 KB: 32 objects x 64 halves, 128B swizzle
 constexpr int kT2StageBytes = kTsAtomsPerStage * kT2AtomBytes;     // 16 KB per CTA
-constexpr int kT2CtrlRegs = 80, kT2EpiRegs = 216;                  // setmaxnreg split (SETS = 2): 128*80 + 256*216 = 65,536
+constexpr int kT2CtrlRegs = 72, kT2EpiRegs = 216;                  // setmaxnreg split (SETS = 2): 128*72 + 256*216 = 64,512 of 65,536
+
+// setmaxnreg moves registers inside the CTA's OWN allocation (SASS: USETMAXREG.TRY_ALLOC.CTAPOOL spins until the
+// CTA pool has them): 384 threads launch with 168 registers each, so the split must not exceed 384 * 168 = 64,512 --
+// a split that sums to the SM's 65,536 never gets its last warp served and the kernel hangs.
+static_assert(128 * kT2CtrlRegs + 256 * kT2EpiRegs <= 384 * 168, "setmaxnreg split exceeds the CTA's register allocation");
+static_assert(kT2CtrlRegs % 8 == 0 && kT2EpiRegs % 8 == 0, "setmaxnreg takes multiples of 8");
 
 constexpr int ts2_threads(int sets) { return 128 + 128 * sets; }
 

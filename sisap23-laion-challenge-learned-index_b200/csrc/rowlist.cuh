@@ -75,14 +75,22 @@ struct RowList {
 // Layout: [k' + kPend][128] entries; pending entries live at k'..k'+cnt-1.  The filter threshold
 // `thr` is the list minimum as of the last prune (stale = lower = conservative).
 constexpr int kPend = 16;
+constexpr int kGrp = 16;          // entries per group of the two-level minimum (k' >= 64)
 
+// Replacing the minimum of a k'-entry list costs a rescan of all k' entries to find the new one: at k' = 128
+// (k = 100) with ~700 replacements per row and chunk that rescan IS the kernel.  For k' >= 64 the list is therefore
+// split into groups of 16 entries whose minima (and positions) live in registers: a replacement rescans the 16
+// entries of one group and then the k'/16 group minima.
 template <int KP>
 struct RowBuf {
+  static constexpr int kG = (KP >= 64) ? KP / kGrp : 1;
   float thr;      // filter: max(lmin at the last prune, seed)
   float lmin;     // minimum of the k' list (kNegInf while it has empty entries)
   float seed;     // external lower bound on the row's final k'-th best score
   int minpos;     // entry holding lmin
   int cnt;        // pending entries
+  float gmin[kG]; // (k' >= 64) minimum of every group of 16 entries ...
+  int gpos[kG];   // ... and the entry holding it
 
   __device__ __forceinline__ void reset(float* sc, int32_t* ps, int row, bool live, float seed_) {
 #pragma unroll 4
@@ -92,6 +100,10 @@ struct RowBuf {
     thr = seed;
     minpos = 0;
     cnt = 0;
+    if constexpr (kG > 1) {
+#pragma unroll
+      for (int g = 0; g < kG; ++g) { gmin[g] = kNegInf; gpos[g] = g * kGrp; }
+    }
   }
   __device__ __forceinline__ void raise_seed(float s) {
     seed = fmaxf(seed, s);
@@ -102,25 +114,48 @@ struct RowBuf {
     ps[(KP + cnt) * kTileQ + row] = pos;
     ++cnt;
   }
+  // overwrite the list minimum with (s, pos) and find the new minimum
+  __device__ __forceinline__ void replace_min(float* sc, int32_t* ps, int row, float s, int32_t pos) {
+    sc[minpos * kTileQ + row] = s;
+    ps[minpos * kTileQ + row] = pos;
+    if constexpr (kG == 1) {
+      float m = sc[row];
+      int mp = 0;
+#pragma unroll
+      for (int j = 1; j < KP; ++j) {
+        const float v = sc[j * kTileQ + row];
+        if (v < m) { m = v; mp = j; }
+      }
+      lmin = m;
+      minpos = mp;
+    } else {
+      const int g = minpos / kGrp;                       // the group that held the minimum: rescan its 16 entries
+      const int base = g * kGrp;
+      float m = sc[base * kTileQ + row];
+      int mp = base;
+#pragma unroll
+      for (int j = 1; j < kGrp; ++j) {
+        const float v = sc[(base + j) * kTileQ + row];
+        if (v < m) { m = v; mp = base + j; }
+      }
+      float bm = 3.0e38f; int bp = 0;
+#pragma unroll
+      for (int gg = 0; gg < kG; ++gg) {                  // (select chains: the arrays stay in registers)
+        gmin[gg] = (gg == g) ? m : gmin[gg];
+        gpos[gg] = (gg == g) ? mp : gpos[gg];
+        if (gmin[gg] < bm) { bm = gmin[gg]; bp = gpos[gg]; }
+      }
+      lmin = bm;
+      minpos = bp;
+    }
+  }
   // warp-collective: merge every row's pending entries into its list
   __device__ __forceinline__ void prune(float* sc, int32_t* ps, int row) {
     const int mx = __reduce_max_sync(0xffffffffu, cnt);
     for (int i = 0; i < mx; ++i) {
       if (i < cnt) {
         const float s = sc[(KP + i) * kTileQ + row];
-        if (s > lmin) {
-          sc[minpos * kTileQ + row] = s;
-          ps[minpos * kTileQ + row] = ps[(KP + i) * kTileQ + row];
-          float m = sc[row];
-          int mp = 0;
-#pragma unroll
-          for (int j = 1; j < KP; ++j) {
-            const float v = sc[j * kTileQ + row];
-            if (v < m) { m = v; mp = j; }
-          }
-          lmin = m;
-          minpos = mp;
-        }
+        if (s > lmin) replace_min(sc, ps, row, s, ps[(KP + i) * kTileQ + row]);
       }
     }
     cnt = 0;
@@ -128,17 +163,7 @@ struct RowBuf {
   }
   // immediate insertion of one candidate that beats the list minimum (no pending entries; per-thread)
   __device__ __forceinline__ void insert_now(float* sc, int32_t* ps, int row, float s, int32_t pos) {
-    sc[minpos * kTileQ + row] = s;
-    ps[minpos * kTileQ + row] = pos;
-    float m = sc[row];
-    int mp = 0;
-#pragma unroll 4
-    for (int j = 1; j < KP; ++j) {
-      const float v = sc[j * kTileQ + row];
-      if (v < m) { m = v; mp = j; }
-    }
-    lmin = m;
-    minpos = mp;
+    replace_min(sc, ps, row, s, pos);
     thr = fmaxf(lmin, seed);
   }
   __device__ __forceinline__ void flush(const float* sc, const int32_t* ps, int row, Cand* out) const {

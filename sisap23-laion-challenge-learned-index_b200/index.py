@@ -146,6 +146,11 @@ class GpuLearnedIndex:
         self.set_option("rescore", rescore)
         if chunk_objects is not None:
             self.set_option("chunk_objects", chunk_objects)
+        env_sets = os.environ.get("LMI_EPI_SETS", "")          # CTA-pair kernel: epilogue warp sets (0 = automatic, 1, 2)
+        if env_sets != "":
+            if env_sets not in ("0", "1", "2"):
+                raise ValueError(f"LMI_EPI_SETS must be 0, 1 or 2, got {env_sets!r}")
+            self.set_option("epi_sets", int(env_sets))
         if world > 1:
             check(self._lib.lmi_set_shard(self._h, rank, world, shard_policy))
         self.rank, self.world = rank, world
