@@ -334,7 +334,21 @@ def torch_running_thresholds(inp, classes, nb, k, device):
     return out
 
 
-def cpu_reference_sample(inp, args, target_seconds, li=None, oracle_parity_queries=0, data_host=None):
+def host_feature_major(data_f16_t, chunk=1 << 20):
+    """[N, d] fp16 tensor -> host ndarray [N, d] laid out feature-major (F-ordered), the layout of the DataFrame block
+    the reference holds data_search in (pandas copies a 2-D array into an F-ordered block).  The transposition runs on
+    the GPU in row chunks; the result is a view of a [d, N] C-ordered host array."""
+    import torch
+    n, d = data_f16_t.shape
+    if data_f16_t.device.type != "cuda":
+        return np.asfortranarray(data_f16_t.numpy())
+    out = np.empty((d, n), dtype=np.float16)
+    for lo in range(0, n, chunk):
+        out[:, lo:lo + chunk] = data_f16_t[lo:lo + chunk].T.contiguous().cpu().numpy()
+    return out.T
+
+
+def cpu_reference_sample(inp, args, target_seconds, li=None, oracle_parity_queries=0, data_host=None, data_fm=None):
     """Times the oracle's rank x category loops (the reference's algorithm, LearnedIndex.py:70-97 / :143-193, with
     ``use_threshold=True`` as search.py:119-128 calls it) on ALL queries but only a subset of categories, then scales
     by the fraction of (query, object) pairs covered.  Cost is additive over categories; every sampled (rank,
@@ -384,6 +398,8 @@ def cpu_reference_sample(inp, args, target_seconds, li=None, oracle_parity_queri
 
     pc_dev = inp["pred_categories"]
     dev = pc_dev.device
+    if data_fm is None:
+        data_fm = host_feature_major(inp["data_f16"])
     sizes = torch.bincount(pc_dev, minlength=C).cpu().numpy()
     m_b = np.bincount(classes[:, :nb].reshape(-1), minlength=C)
     pairs_all = float((sizes * m_b).sum())
@@ -397,12 +413,13 @@ def cpu_reference_sample(inp, args, target_seconds, li=None, oracle_parity_queri
     seq = [order[i] for i in sorted(range(len(order)), key=lambda i: abs(i - mid))]
     for c in seq:
         rows = torch.nonzero(pc_dev == int(c)).squeeze(1)
-        # the reference keeps data_search in a DataFrame, whose block is feature-major, and gathers the bucket's rows from
-        # it on every (rank, category) call (LearnedIndex.py:152/168): the sample holds the bucket the same way so that
-        # gather stays inside the timed region (calibration: scripts/calibrate_cpu_baseline.py)
-        data_c = np.asfortranarray(inp["data_f16"][rows].cpu().numpy())
         rows_h = rows.cpu().numpy()
-        table = O.BucketTable(np.full(rows.shape[0], int(c)), 1)
+        # the reference keeps data_search in a DataFrame, whose block is feature-major, and gathers the bucket's rows from
+        # the WHOLE frame on every (rank, category) call (LearnedIndex.py:152/168): the timed calls gather from a
+        # feature-major host array of the whole dataset in the same way (calibration against the unmodified reference:
+        # scripts/calibrate_cpu_baseline.py)
+        data_c = data_fm
+        table = O.BucketTable.single(int(c), rows_h, 1)
         per_rank = []
         s = time.time()
         for rank in range(nb):                                                   # LearnedIndex.py:70
@@ -424,8 +441,7 @@ def cpu_reference_sample(inp, args, target_seconds, li=None, oracle_parity_queri
                 gd, ga = li.search_single(None, None, q16, cats, k=k, threshold_dist=thr)
                 ok = routed[~flagged[routed]]                                     # rows the reference's '<k' defect (D1) touched are skipped
                 cat_par["d1_rows_skipped"] += int(flagged[routed].sum())
-                od, oa = d[ok], a[ok].astype(np.int64)
-                oa = np.where(oa > 0, rows_h[np.maximum(oa - 1, 0)] + 1, 0)      # bucket-local label -> dataset label (row + 1)
+                od, oa = d[ok], a[ok].astype(np.int64)                           # dataset labels (row + 1) on both sides
                 live = od < 10000.0                                               # pruned slots carry arbitrary ids in the reference
                 oa = np.where(live, oa, 0)
                 g_d, g_a = gd[ok], ga[ok].astype(np.int64)
@@ -729,7 +745,7 @@ def run_b200(args):
     # ---- e2e_dropin: the reference-facing Python call with the reference's argument types (search.py:71-72, 83-84,
     #      119-128): DataFrames with 1-based labels, PAGEABLE numpy queries; timed = 2nd and later calls of
     #      GpuLearnedIndex.search (the first builds the store from the frame, reported as store_build_seconds_host) ----
-    dropin = None
+    dropin, data_fm = None, None
     if data_host is not None and not args.no_dropin:
         import pandas as pd
         t0 = time.time()
@@ -758,12 +774,12 @@ def run_b200(args):
                       store_build_seconds_host=t_first, dataframe_seconds=t_frame,
                       frame_layout="feature-major block uploaded as it lies (lmi_store_append_strided)")
         li = li2
-        del data_search
+        data_fm = data_search.to_numpy()                                        # the frame's own feature-major block (a view)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_reference_sample(inp, args, args.cpu_seconds, li=li, oracle_parity_queries=args.oracle_parity_queries,
-                                   data_host=data_host)
-    del data_host
+                                   data_host=data_host, data_fm=data_fm)
+    del data_host, data_fm
 
     if rank == 0:
         line = {

@@ -152,6 +152,13 @@ int lmi_search_rank(lmi_index* idx, const uint16_t* q_f16, int64_t nq,
 int64_t lmi_partial_bytes(int64_t nq, int k);
 int lmi_search_partial_device(lmi_index* idx, const float* q_nav_dev, const uint16_t* q_f16_dev,
                               int64_t nq, int n_buckets, int k, void* partial_dev, void* stream);
+/* The same with the bucket lists supplied by the caller (int32 [nq, n_buckets], device; ids outside [0, C) match no
+ * bucket): lets every rank navigate only its slice of the queries (lmi_navigate_device) and all-gather the lists
+ * (nq * n_buckets * 4 bytes) instead of navigating all queries on every rank. */
+int lmi_navigate_device(lmi_index* idx, const float* q_nav_dev, int64_t nq, int n_top,
+                        int32_t* out_classes_dev, void* stream);
+int lmi_search_partial_classes_device(lmi_index* idx, const int32_t* classes_dev, const uint16_t* q_f16_dev,
+                                      int64_t nq, int n_buckets, int k, void* partial_dev, void* stream);
 /* gathered_dev: `world` partials back to back (rank-major). */
 int lmi_merge_partials_device(lmi_index* idx, const void* gathered_dev, int world, int64_t nq,
                               int k, double* out_dists_dev, uint32_t* out_ids_dev, void* stream);

@@ -100,6 +100,17 @@ class BucketTable:
         self.bounds = np.append(starts, pc.shape[0])
         self.id_base = id_base
 
+    @classmethod
+    def single(cls, cat, rows, id_base=1):
+        """A table holding ONE category whose objects are the given (ascending) dataset rows -- what a bounded CPU
+        sample iterates when it times single categories of a large dataset."""
+        t = cls.__new__(cls)
+        t.order = np.asarray(rows, dtype=np.int64)
+        t.cats = np.array([int(cat)])
+        t.bounds = np.array([0, t.order.shape[0]])
+        t.id_base = id_base
+        return t
+
     def __iter__(self):
         for i, cat in enumerate(self.cats):
             yield int(cat), self.order[self.bounds[i]:self.bounds[i + 1]]

@@ -17,7 +17,7 @@ SYMBOLS = [
     "lmi_set_mlp", "lmi_store_begin", "lmi_store_append", "lmi_store_append_strided",
     "lmi_store_end", "lmi_store_save", "lmi_store_load", "lmi_set_buckets",
     "lmi_navigate", "lmi_predict", "lmi_search", "lmi_search_device", "lmi_search_rank",
-    "lmi_partial_bytes", "lmi_search_partial_device", "lmi_merge_partials_device", "lmi_get_stats",
+    "lmi_partial_bytes", "lmi_search_partial_device", "lmi_navigate_device", "lmi_search_partial_classes_device", "lmi_merge_partials_device", "lmi_get_stats",
     "lmi_get_bucket_ptr", "lmi_rescore_kernel_name",
 ]
 
@@ -77,6 +77,8 @@ def load() -> C.CDLL:
     lib.lmi_partial_bytes.argtypes = [i64, i]
     lib.lmi_partial_bytes.restype = i64
     lib.lmi_search_partial_device.argtypes = [p, vp, vp, i64, i, i, vp, vp]
+    lib.lmi_navigate_device.argtypes = [p, vp, i64, i, vp, vp]
+    lib.lmi_search_partial_classes_device.argtypes = [p, vp, vp, i64, i, i, vp, vp]
     lib.lmi_merge_partials_device.argtypes = [p, vp, i, i64, i, vp, vp, vp]
     lib.lmi_get_stats.argtypes = [p, C.POINTER(LmiStats)]
     lib.lmi_get_bucket_ptr.argtypes = [p, vp]

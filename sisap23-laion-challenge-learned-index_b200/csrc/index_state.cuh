@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <string.h>
 #include <algorithm>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 #include <string>
 #include <vector>

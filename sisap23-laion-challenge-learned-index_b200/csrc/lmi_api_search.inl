@@ -12,19 +12,56 @@ static bool host_ptr_is_pinned(const void* p) {
   return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
 }
 
-static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
-  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-  const int n_thr = (int)std::min<size_t>(std::min(8u, hw), bytes / ((size_t)1 << 20) + 1);
-  if (n_thr <= 1) { memcpy(dst, src, bytes); return; }
-  std::vector<std::thread> pool;
-  auto work = [&](int t) {
-    const size_t lo = bytes * t / n_thr / 64 * 64, hi = (t + 1 == n_thr) ? bytes : bytes * (t + 1) / n_thr / 64 * 64;
-    memcpy((char*)dst + lo, (const char*)src + lo, hi - lo);
-  };
-  for (int t = 1; t < n_thr; ++t) pool.emplace_back(work, t);
-  work(0);
-  for (auto& th : pool) th.join();
-}
+// A few persistent host threads that copy slices of a buffer (created on first use, shared by all indexes of the
+// process; spawning threads per call costs more than the copy of a 15 MB query batch).
+class CopyPool {
+ public:
+  static CopyPool& get() { static CopyPool* p = new CopyPool(); return *p; }     // never destroyed: its helpers outlive main()
+  void copy(void* dst, const void* src, size_t bytes) {
+    if (bytes < ((size_t)1 << 20) || workers_.empty()) { memcpy(dst, src, bytes); return; }
+    std::unique_lock<std::mutex> lk(mu_);
+    dst_ = (char*)dst; src_ = (const char*)src; bytes_ = bytes;
+    parts_ = (int)workers_.size() + 1;
+    next_ = 0; left_ = parts_;
+    ++gen_;
+    cv_.notify_all();
+    lk.unlock();
+    drain();
+    lk.lock();
+    done_.wait(lk, [&] { return left_ == 0; });
+  }
+ private:
+  CopyPool() {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const int n = (int)std::min(7u, hw > 1 ? hw - 1 : 0u);
+    for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
+    for (auto& t : workers_) t.detach();        // process-lifetime helpers (no join at exit: they only wait on cv_)
+  }
+  void drain() {
+    for (;;) {
+      int p;
+      { std::lock_guard<std::mutex> g(mu_); if (next_ >= parts_) return; p = next_++; }
+      const size_t lo = bytes_ * p / parts_ / 64 * 64, hi = (p + 1 == parts_) ? bytes_ : bytes_ * (p + 1) / parts_ / 64 * 64;
+      memcpy(dst_ + lo, src_ + lo, hi - lo);
+      { std::lock_guard<std::mutex> g(mu_); if (--left_ == 0) done_.notify_all(); }
+    }
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      { std::unique_lock<std::mutex> lk(mu_); cv_.wait(lk, [&] { return gen_ != seen; }); seen = gen_; }
+      drain();
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> workers_;
+  char* dst_ = nullptr; const char* src_ = nullptr; size_t bytes_ = 0;
+  int parts_ = 0, next_ = 0, left_ = 0;
+  uint64_t gen_ = 0;
+};
+
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) { CopyPool::get().copy(dst, src, bytes); }
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is per function AND per device: it is set before every launch (a few
 // microseconds) instead of being cached per process, so a second index on another GPU, or another index with a
@@ -144,7 +181,7 @@ static int choose_chunk(const lmi_index* idx, int64_t nq, int nb, int KP) {
 // list: navigation (search) or caller-supplied categories (search_rank, nb = 1).
 static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls64_dev, const uint16_t* q16_dev,
                       int64_t nq, int nb, int k, const double* thr_dev, int mode, double* out_d, uint32_t* out_i,
-                      Partial* out_p, cudaStream_t st, cudaEvent_t q16_ready = nullptr) {
+                      Partial* out_p, cudaStream_t st, cudaEvent_t q16_ready = nullptr, const int32_t* cls32_dev = nullptr) {
   if (!idx->has_store) return set_error(LMI_ERR_STATE, "bucket store not built (lmi_store_* / lmi_set_buckets)");
   if (q_nav_dev && !idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");   // LearnedIndex.py:60
   if (nq <= 0 || nq > (1 << 24)) return set_error(LMI_ERR_ARG, "nq out of range");
@@ -214,7 +251,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   if (timing) LMI_CUDA(cudaEventRecord(idx->ev[0], st));
   // ---- K1 navigation ----
   int32_t* top = idx->top_cls.as<int32_t>();
-  if (q_nav_dev) {
+  if (cls32_dev) {
+    top = const_cast<int32_t*>(cls32_dev);               // bucket lists navigated elsewhere (multi-GPU: every rank navigates a slice)
+  } else if (q_nav_dev) {
     int rc = launch_nav(idx, q_nav_dev, nq, nb, top, nullptr, st);
     if (rc != LMI_OK) return rc;
   } else {
@@ -353,11 +392,19 @@ int lmi_search(lmi_index* idx, const float* q_nav, const uint16_t* q_f16, int64_
     src_nav = idx->pin_in.p;
   }
   LMI_CUDA(cudaMemcpyAsync(idx->ws_qnav.p, src_nav, b_nav, cudaMemcpyHostToDevice, st));
-  if (src_nav != q_nav) {                                                // (navigation is already running while the 4x larger block is gathered)
-    src_q16 = (char*)idx->pin_in.p + b_nav;
-    parallel_memcpy(const_cast<void*>(src_q16), q_f16, b_q16);
+  if (src_nav != q_nav) {
+    // navigation is already running while the 4x larger block is gathered; 4 pieces so the H2D copy of one piece
+    // overlaps the host-side gather of the next
+    char* stage = (char*)idx->pin_in.p + b_nav;
+    const int n_piece = b_q16 >= ((size_t)4 << 20) ? 4 : 1;
+    for (int c = 0; c < n_piece; ++c) {
+      const size_t lo = b_q16 * c / n_piece / 256 * 256, hi = (c + 1 == n_piece) ? b_q16 : b_q16 * (c + 1) / n_piece / 256 * 256;
+      parallel_memcpy(stage + lo, (const char*)q_f16 + lo, hi - lo);
+      LMI_CUDA(cudaMemcpyAsync((char*)idx->ws_q16.p + lo, stage + lo, hi - lo, cudaMemcpyHostToDevice, idx->copy_stream));
+    }
+  } else {
+    LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, src_q16, b_q16, cudaMemcpyHostToDevice, idx->copy_stream));
   }
-  LMI_CUDA(cudaMemcpyAsync(idx->ws_q16.p, src_q16, b_q16, cudaMemcpyHostToDevice, idx->copy_stream));
   LMI_CUDA(cudaEventRecord(idx->ev_q16, idx->copy_stream));
   int rc = run_search(idx, idx->ws_qnav.as<float>(), nullptr, idx->ws_q16.as<uint16_t>(), nq, n_buckets, k, nullptr, 0,
                       idx->ws_out_d.as<double>(), idx->ws_out_i.as<uint32_t>(), nullptr, st, idx->ev_q16);
@@ -397,6 +444,22 @@ int lmi_search_partial_device(lmi_index* idx, const float* q_nav_dev, const uint
   if (!idx || !q_nav_dev || !q_f16_dev || !partial_dev) return set_error(LMI_ERR_ARG, "NULL argument");
   return run_search(idx, q_nav_dev, nullptr, q_f16_dev, nq, n_buckets, k, nullptr, 1, nullptr, nullptr,
                     reinterpret_cast<Partial*>(partial_dev), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int lmi_navigate_device(lmi_index* idx, const float* q_nav_dev, int64_t nq, int n_top, int32_t* out_classes_dev, void* stream) {
+  if (!idx || !q_nav_dev || !out_classes_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (!idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");
+  if (n_top < 1 || n_top > idx->C) return set_error(LMI_ERR_ARG, "n_top must be in [1, n_categories]");
+  if (nq < 0) return set_error(LMI_ERR_ARG, "nq < 0");
+  LMI_CUDA(cudaSetDevice(idx->device));
+  return launch_nav(idx, q_nav_dev, nq, n_top, out_classes_dev, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int lmi_search_partial_classes_device(lmi_index* idx, const int32_t* classes_dev, const uint16_t* q_f16_dev, int64_t nq,
+                                      int n_buckets, int k, void* partial_dev, void* stream) {
+  if (!idx || !classes_dev || !q_f16_dev || !partial_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  return run_search(idx, nullptr, nullptr, q_f16_dev, nq, n_buckets, k, nullptr, 1, nullptr, nullptr,
+                    reinterpret_cast<Partial*>(partial_dev), reinterpret_cast<cudaStream_t>(stream), nullptr, classes_dev);
 }
 
 int lmi_merge_partials_device(lmi_index* idx, const void* gathered_dev, int world, int64_t nq, int k, double* out_dists_dev,

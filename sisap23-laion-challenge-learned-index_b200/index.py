@@ -375,6 +375,21 @@ class GpuLearnedIndex:
         check(self._lib.lmi_search_partial_device(self._h, C.c_void_p(q_nav_t.data_ptr()), C.c_void_p(q_f16_t.data_ptr()),
                                                   nq, int(n_buckets), int(k), C.c_void_p(partial_t.data_ptr()), C.c_void_p(st)))
 
+    def navigate_device(self, q_nav_t, n_top, out_classes_t):
+        """top-n_top bucket ids (int32 [rows, n_top], device) of device-resident navigation vectors."""
+        import torch
+        st = torch.cuda.current_stream(q_nav_t.device).cuda_stream
+        check(self._lib.lmi_navigate_device(self._h, C.c_void_p(q_nav_t.data_ptr()), int(q_nav_t.shape[0]), int(n_top),
+                                            C.c_void_p(out_classes_t.data_ptr()), C.c_void_p(st)))
+
+    def search_partial_classes_device(self, classes_t, q_f16_t, n_buckets, k, partial_t):
+        """search_partial_device with caller-supplied bucket lists (int32 [nq, n_buckets], device)."""
+        import torch
+        nq = int(q_f16_t.shape[0])
+        st = torch.cuda.current_stream(q_f16_t.device).cuda_stream
+        check(self._lib.lmi_search_partial_classes_device(self._h, C.c_void_p(classes_t.data_ptr()), C.c_void_p(q_f16_t.data_ptr()),
+                                                          nq, int(n_buckets), int(k), C.c_void_p(partial_t.data_ptr()), C.c_void_p(st)))
+
     def merge_partials_device(self, gathered_t, world, nq, k, out):
         import torch
         st = torch.cuda.current_stream(gathered_t.device).cuda_stream

@@ -77,19 +77,22 @@ def test_search_rank_threshold_vs_oracle(case, k):
     li = _index(c)                                  # library default kernel
     d0, a0 = li.search_single(None, c["data_f16"], c["queries_f16"], c["classes"][:, 0], k=k)
     rng = np.random.default_rng(5)
-    for cats, thr in ((c["classes"][:, 1], d0.max(axis=1)),
-                      (c["classes"][:, 0], d0[np.arange(d0.shape[0]), rng.integers(0, k, d0.shape[0])])):
+    # thresholds lie BETWEEN two distances of the row (a threshold that equals a candidate's distance to the last bit
+    # would fall on either side of the strict '<' depending on float64 summation order)
+    j = rng.integers(1, k, d0.shape[0])
+    mid = 0.5 * (d0[np.arange(d0.shape[0]), j - 1] + d0[np.arange(d0.shape[0]), j])
+    sep = (d0[np.arange(d0.shape[0]), j] - d0[np.arange(d0.shape[0]), j - 1]) > 1e-9
+    for cats, thr, ok in ((c["classes"][:, 1], d0.max(axis=1), np.ones(d0.shape[0], bool)), (c["classes"][:, 0], mid, sep)):
         d, a = li.search_single(None, c["data_f16"], c["queries_f16"], cats, k=k, threshold_dist=thr)
         od, oa = O.search_intended(cats[:, None], c["data_f16"], c["queries_f16"], c["pred_categories"], 1, k, thresholds=thr)
-        # a distance that equals its threshold to the last bit may fall on either side of the strict '<'
-        # (float64 summation order): such rows are excluded, there must be next to none
-        edge = (np.abs(od - thr[:, None]) < 1e-12).any(axis=1) | (np.abs(d - thr[:, None]) < 1e-12).any(axis=1)
-        assert edge.mean() < 0.02
-        ok = ~edge
+        ok = ok & ~(np.abs(od - thr[:, None]) < 1e-12).any(axis=1)
+        assert ok.mean() > 0.95
         assert_ids_equal_up_to_ties(a[ok], d[ok], oa[ok], od[ok], what=f"search_rank threshold k={k}")
         np.testing.assert_allclose(d[ok], od[ok], rtol=1e-3, atol=1e-9)
         assert (a[d == 10000.0] == 0).all()
         assert li.stats()["n_uncertified"] == 0
+    # second case: exactly j survivors per row (everything below the midpoint)
+    assert ((d[ok] < 10000.0).sum(axis=1) == j[ok]).all()
 
 
 @pytest.mark.parametrize("nb,k", [(4, 10), (3, 50), (2, 100)])
@@ -186,6 +189,43 @@ def test_sharded_merge_equals_single(case, world, policy, nb, k):
     torch.cuda.synchronize()
     assert (out[1].cpu().numpy().view(np.uint32) == ref_a).all()
     assert (out[0].cpu().numpy() == ref_d).all()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sliced_navigation_equals_replicated(case, world):
+    """Multi-GPU navigation split (DistributedSearch(slice_navigation=True)): every rank navigates rows
+    [r*per, (r+1)*per) with lmi_navigate_device, the int32 bucket lists are concatenated (the all-gather) and fed to
+    lmi_search_partial_classes_device.  Lists and partial results must equal what full navigation on the rank gives."""
+    import torch
+    from lmi_b200.index import GpuLearnedIndex
+    c = case
+    nb, k = 4, 10
+    nq = c["queries_f16"].shape[0]
+    qn = torch.from_numpy(c["queries_nav"]).cuda()
+    qs = torch.from_numpy(c["queries_f16"]).cuda()
+    per = (nq + world - 1) // world
+    li = GpuLearnedIndex(c["C"], rank=1, world=world).set_model(c["weights"], c["biases"])
+    li.prepare(c["data_f16"], c["pred_categories"])
+    every = torch.full((world * per, nb), -1, dtype=torch.int32, device="cuda")
+    for r in range(world):
+        lo, hi = min(nq, r * per), min(nq, (r + 1) * per)
+        if hi > lo:
+            li.navigate_device(qn[lo:hi], nb, every[r * per:r * per + (hi - lo)])
+    _, full = li.model.predict_proba(c["queries_nav"], n_top=nb)
+    assert (every[:nq].cpu().numpy() == full).all()
+    p_ref = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device="cuda")
+    li.search_partial_device(qn, qs, nb, k, p_ref)
+    p_new = torch.empty_like(p_ref)
+    li.search_partial_classes_device(every, qs, nb, k, p_new)
+    torch.cuda.synchronize()
+    assert torch.equal(p_new, p_ref)
+    # ids outside [0, C) match no bucket: a list of -1 gives an empty row
+    every[:8] = -1
+    li.search_partial_classes_device(every, qs, nb, k, p_new)
+    torch.cuda.synchronize()
+    from lmi_b200.shard import PARTIAL_DTYPE
+    part = np.frombuffer(p_new.cpu().numpy().tobytes(), dtype=PARTIAL_DTYPE).reshape(nq, k)
+    assert (part["id"][:8] == 0).all() and (part["dist"][:8] == 10000.0).all()
 
 
 @pytest.mark.parametrize("world", [2, 5])

@@ -55,7 +55,19 @@ def _worker(rank, world, port, tag, policy, out_dir):
     try:
         g = load_golden(tag)
         results = {}
+        from oracle import lmi_oracle as O
         for nb in g["bucket_list"]:
+            # navigation split (DistributedSearch.slice_navigation): every rank navigates its slice of the queries,
+            # ONE all-gather of [per, nb] int32 blocks rebuilds the bucket lists of the whole batch
+            nq = g["queries_nav"].shape[0]
+            per, lo, hi = S.query_slice_of_rank(nq, rank, world)
+            mine = np.full((per, nb), -1, dtype=np.int32)
+            if hi > lo:
+                mine[:hi - lo] = O.predict_proba(g["queries_nav"][lo:hi], g["weights"], g["biases"])[1][:, :nb]
+            every = torch.empty(world * per, nb, dtype=torch.int32)
+            dist.all_gather_into_tensor(every, torch.from_numpy(mine))
+            every = every.numpy()
+            assert (every[:nq] == g["classes"][:, :nb]).all() and (every[nq:] == -1).all()
             part, keep = _partial_for_rank(g, nb, rank, world, policy)
             # every object is held by exactly one rank
             cnt = torch.from_numpy(keep.astype(np.int32))
