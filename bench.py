@@ -825,8 +825,9 @@ def run_reference(args):
     per_step = max(2.0, min(args.cpu_seconds, 150.0 / (steps + args.warmup)))
     vals, last = [], None
     t0 = time.time()
+    data_fm = host_feature_major(inp["data_f16"])          # the layout the reference holds data_search in (a DataFrame block)
     for i in range(args.warmup + steps):
-        last = cpu_reference_sample(inp, args, per_step)
+        last = cpu_reference_sample(inp, args, per_step, data_fm=data_fm)
         if i >= args.warmup:
             vals.append(last["value"])
     v = float(np.mean(vals))

@@ -20,6 +20,7 @@ namespace lmi {
 
 constexpr int kFinWarps = 8;
 constexpr int kFinRegE = 24;          // entries per lane of the register-resident selection (<= 768 entries per query)
+constexpr int kFinRegBig = 48;        // same for the bisection selection used when k' >= 64 (<= 1536 entries per query)
 constexpr int kFinMaxVec = 128;       // uint4 per row, d <= 1024
 constexpr double kCertEps = 2e-5;       // bound used by the exactness certificate
 
@@ -88,6 +89,78 @@ __device__ __forceinline__ double fin_load_query(const uint4* __restrict__ qrow,
   return (qq == 0.0) ? 1.0 : sqrt(qq);
 }
 
+// order-preserving uint32 image of an fp32 score (0 = invalid entry)
+__device__ __forceinline__ uint32_t fin_key(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float fin_unkey(uint32_t u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+// Selection of the R best of up to 32 x NE register-resident entries by BISECTION on the score (k' >= 64, i.e.
+// k = 100: R rounds of warp arg-max cost R x (NE selects + 10 shuffles); a 32-step binary search for the R-th largest
+// key costs 32 x (NE compares + 5 shuffles), then one pass of ballots compacts the survivors).  Ties at the R-th
+// score go to the lowest entry number (rank, list, position order), like the round-based selection.
+// Returns the number selected; survivors land in s_pos/s_rank/s_dist in entry order; score_R = R-th best score.
+template <int NE>
+__device__ __forceinline__ int fin_select_bisect(int lane, int R, int total, const int32_t* s_rcum, const int64_t* s_rbeg,
+                                                 const Cand* __restrict__ plists, int32_t* s_pos, uint32_t* s_rank,
+                                                 double* s_dist, float& score_R) {
+  uint32_t key[NE]; int32_t ep[NE];
+  int valid = 0;
+#pragma unroll
+  for (int u = 0; u < NE; ++u) {
+    const int g = lane + 32 * u;                   // entry number in (rank, list, position) order
+    key[u] = 0u; ep[u] = -1;
+    if (g < total) {
+      int r = 0;
+      while (g >= s_rcum[r + 1]) ++r;
+      const Cand c = plists[s_rbeg[r] + (g - s_rcum[r])];
+      if (c.pos >= 0) { key[u] = fin_key(c.score); ep[u] = c.pos; ++valid; }
+    }
+  }
+  valid = __reduce_add_sync(0xffffffffu, valid);
+  uint32_t T = 1u;                                 // everything valid has key >= 1
+  int need_eq = 0x7fffffff;
+  if (valid > R) {
+    T = 0u;
+    for (int bit = 31; bit >= 0; --bit) {          // largest T with count(key >= T) >= R
+      const uint32_t cand = T | (1u << bit);
+      int c = 0;
+#pragma unroll
+      for (int u = 0; u < NE; ++u) c += (key[u] >= cand) ? 1 : 0;
+      c = __reduce_add_sync(0xffffffffu, c);
+      if (c >= R) T = cand;
+    }
+    int gt = 0;
+#pragma unroll
+    for (int u = 0; u < NE; ++u) gt += (key[u] > T) ? 1 : 0;
+    gt = __reduce_add_sync(0xffffffffu, gt);
+    need_eq = R - gt;                              // >= 1 entries equal to T complete the selection
+  }
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int out = 0, eq_seen = 0;
+#pragma unroll
+  for (int u = 0; u < NE; ++u) {
+    const bool is_eq = key[u] == T && key[u] != 0u;
+    const uint32_t m_eq = __ballot_sync(0xffffffffu, is_eq);
+    const bool sel = key[u] != 0u && (key[u] > T || (is_eq && eq_seen + __popc(m_eq & lt_mask) < need_eq));
+    const uint32_t m_sel = __ballot_sync(0xffffffffu, sel);
+    if (sel) {
+      const int o = out + __popc(m_sel & lt_mask);
+      const int g = lane + 32 * u;
+      int r = 0;
+      while (g >= s_rcum[r + 1]) ++r;
+      s_pos[o] = ep[u]; s_rank[o] = (uint32_t)r; s_dist[o] = (double)fin_unkey(key[u]);
+    }
+    out += __popc(m_sel);
+    eq_seen += __popc(m_eq);
+  }
+  score_R = fin_unkey(T);
+  return out;
+}
+
 // mode 0: write out_dists/out_ids [nq,k];  mode 1: write Partial [nq,k]
 __global__ void __launch_bounds__(kFinWarps * 32)
 finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
@@ -147,11 +220,17 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   // Fast path (the usual case: one rank group and at most 32 x kFinRegE entries, e.g. 4 ranks x 3 chunks
   // x k' = 16): every lane reads its entries once and the R rounds run on registers.
   bool fast = (n_groups == 1);
+  bool bisect = false;
+  float score_R_sel = 0.f;                             // R-th best fp32 score (set by whichever selection ran)
   if (fast) {
     load_ranges(0);
-    fast = s_rcum[warp][nb] <= 32 * kFinRegE;
+    bisect = R >= 64 && s_rcum[warp][nb] <= 32 * kFinRegBig;
+    fast = !bisect && s_rcum[warp][nb] <= 32 * kFinRegE;
   }
-  if (fast) {
+  if (bisect) {
+    n_sel = fin_select_bisect<kFinRegBig>(lane, R, s_rcum[warp][nb], s_rcum[warp], s_rbeg[warp], plists,
+                                          s_pos[warp], s_rank[warp], s_dist[warp], score_R_sel);
+  } else if (fast) {
     const int total = s_rcum[warp][nb];
     float es[kFinRegE]; int32_t ep[kFinRegE];
 #pragma unroll
@@ -244,12 +323,22 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   // ---- float64 re-scoring of the survivors ---------------------------------------------------
   // The candidate rows are random 1.5 KB reads from HBM: 4 candidates are in flight per warp (8 lanes
   // each, 6 x 16 bytes per lane outstanding) instead of one after the other.
+  if (n_sel == 0) {
+    // nothing to re-score (on a shard most queries probe no local bucket): emit the empty row without touching
+    // the query vector or the store
+    for (int o = lane; o < k; o += 32) {
+      if (mode == 0) { out_dists[qi * k + o] = kEmptyDist; out_ids[qi * k + o] = 0u; }
+      else { Partial p; p.dist = kEmptyDist; p.id = 0u; p.rank = 0xffffffffu; out_partial[qi * k + o] = p; }
+    }
+    return;
+  }
   const int vec = d / 8;                                  // uint4 per row (d is a multiple of 64)
   const uint4* qrow = reinterpret_cast<const uint4*>(q + (size_t)qi * d);
   uint4* sq = s_q[warp];
   const double qn = fin_load_query(qrow, sq, vec, lane);
   double max_err = 0.0;
-  const float score_R = (n_sel == R) ? (float)s_dist[warp][R - 1] : 0.f;     // before the scores are overwritten
+  // (the round-based selections leave the scores in descending order; read before they are overwritten)
+  const float score_R = (n_sel == R) ? (bisect ? score_R_sel : (float)s_dist[warp][R - 1]) : 0.f;
   __syncwarp();
   const int grp = lane >> 3, sub = lane & 7;
   for (int t0 = 0; t0 < n_sel; t0 += 4) {

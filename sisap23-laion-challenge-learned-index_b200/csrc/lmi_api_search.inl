@@ -173,7 +173,13 @@ static int choose_chunk(const lmi_index* idx, int64_t nq, int nb, int KP) {
   const double qtiles = (double)nq * nb * idx->pair_fraction / kTileQ + 0.5 * (double)idx->n_nonempty;
   const double avg_bucket = (double)idx->n_local / (double)std::max<int64_t>(idx->n_nonempty, 1);
   double c = qtiles * avg_bucket / target;
-  c = std::min(std::max(c, 1024.0), (double)(1 << 22));
+  // Floor: an item must be long enough to amortise what it pays once (128 query rows into tensor memory, pipeline fill,
+  // one partial list per row for K4).  Measured per rank of an 8-way bucket shard (profiles/r2c_shard_emulate_n8_buckets.json):
+  // 4,096-object chunks 1.33 ms per partial search (K3 0.93 + finalize 0.22), 8,192: 1.16, 16,384: 1.15 (0.83 + 0.13),
+  // 32,768: 1.27.  For k' >= 64 the K4 selection runs on registers up to 1,536 entries per query: no more than
+  // 1536 / (nb * k') chunks per bucket where the buckets allow it.
+  const double floor_c = (KP >= 64) ? std::max(12288.0, (double)idx->h_sizes_sorted[0] * nb * KP / 1536.0) : 12288.0;
+  c = std::min(std::max(c, floor_c), (double)(1 << 22));
   return (int)(((int64_t)c + 255) / 256 * 256);
 }
 
