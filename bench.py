@@ -595,26 +595,31 @@ def run_b200(args):
         nbytes = li.partial_bytes(nq, k)
         part = torch.empty(nbytes, dtype=torch.uint8, device=device)
         gathered = torch.empty(world * nbytes, dtype=torch.uint8, device=device)
-        evs = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        acc = np.zeros(3)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        acc = np.zeros(4)
         reps = 10
         for _ in range(reps):
             barrier()
-            evs[0].record(); li.search_partial_device(qn, qs, nb, k, part)
-            evs[1].record(); dist.all_gather_into_tensor(gathered, part)
-            evs[2].record(); li.merge_partials_device(gathered, world, nq, k, out)
-            evs[3].record(); torch.cuda.synchronize()
-            acc += [evs[i].elapsed_time(evs[i + 1]) for i in range(3)]
-        mine = torch.tensor(list(acc / reps) + [st_loop["ms_rescore_avg"]], device=device, dtype=torch.float64)
-        allr = torch.empty(world, 4, device=device, dtype=torch.float64)
+            evs[0].record(); every = ds.navigate_sliced(qn, nb)                   # own slice through K1 + all-gather of the bucket lists
+            evs[1].record(); li.search_partial_classes_device(every, qs, nb, k, part)
+            evs[2].record(); dist.all_gather_into_tensor(gathered, part)
+            evs[3].record(); li.merge_partials_device(gathered, world, nq, k, out)
+            evs[4].record(); torch.cuda.synchronize()
+            acc += [evs[i].elapsed_time(evs[i + 1]) for i in range(4)]
+        st_b = li.stats()
+        mine = torch.tensor(list(acc / reps) + [st_loop["ms_rescore_avg"], st_b["ms_plan"], st_b["ms_finalize"]], device=device, dtype=torch.float64)
+        allr = torch.empty(world, 7, device=device, dtype=torch.float64)
         dist.all_gather_into_tensor(allr, mine)
         allr = allr.cpu().numpy()
-        shard_breakdown = dict(partial_search_ms_per_rank=[round(float(v), 4) for v in allr[:, 0]],
-                               all_gather_ms_max=float(allr[:, 1].max()), all_gather_ms_min=float(allr[:, 1].min()),
-                               merge_ms_max=float(allr[:, 2].max()),
-                               rescore_ms_per_rank=[round(float(v), 4) for v in allr[:, 3]],
-                               note="ranks start each repetition together (barrier); the all-gather time of a rank includes "
-                                    "waiting for the slowest rank's partial search")
+        shard_breakdown = dict(navigate_slice_plus_allgather_ms_max=float(allr[:, 0].max()),
+                               partial_search_ms_per_rank=[round(float(v), 4) for v in allr[:, 1]],
+                               all_gather_ms_max=float(allr[:, 2].max()), all_gather_ms_min=float(allr[:, 2].min()),
+                               merge_ms_max=float(allr[:, 3].max()),
+                               rescore_ms_per_rank=[round(float(v), 4) for v in allr[:, 4]],
+                               plan_ms_max=float(allr[:, 5].max()), finalize_ms_max=float(allr[:, 6].max()),
+                               note="ranks start each repetition together (barrier); a collective's time on a rank includes "
+                                    "waiting for the slowest rank; partial_search = plan + rescoring + finalize (+ exact fallback) "
+                                    "on the gathered bucket lists")
 
     # ---- end to end: host buffers in, host buffers out, copies inside the timed region ----
     # N=1: the reference-facing C-ABI call lmi_search (pinned host inputs; H2D, search, D2H inside the call).

@@ -123,7 +123,7 @@ __device__ __forceinline__ int fin_select_bisect(int lane, int R, int total, con
   valid = __reduce_add_sync(0xffffffffu, valid);
   uint32_t T = 1u;                                 // everything valid has key >= 1
   int need_eq = 0x7fffffff;
-  if (valid > R) {
+  if (valid >= R) {                                // (valid == R: T = the smallest key, which the certificate needs)
     T = 0u;
     for (int bit = 31; bit >= 0; --bit) {          // largest T with count(key >= T) >= R
       const uint32_t cand = T | (1u << bit);

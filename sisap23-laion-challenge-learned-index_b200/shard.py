@@ -133,21 +133,28 @@ class DistributedSearch:
                           torch.empty(self.world * nbytes, dtype=torch.uint8, device=dev))
         part, gathered = self._bufs
         if self.slice_navigation:
-            W = self.world
-            r = self.dist.get_rank(self.group)
-            per, lo, hi = query_slice_of_rank(nq, r, W)
-            if self._cls is None or self._cls[0].shape != (per, n_buckets):
-                self._cls = (torch.full((per, n_buckets), -1, dtype=torch.int32, device=dev),
-                             torch.empty(W * per, n_buckets, dtype=torch.int32, device=dev))
-            mine, every = self._cls
-            if hi > lo:
-                self.li.navigate_device(q_nav_t[lo:hi], n_buckets, mine)
-            self.dist.all_gather_into_tensor(every, mine, group=self.group)     # bucket lists: nq x n_buckets x 4 bytes
+            every = self.navigate_sliced(q_nav_t, n_buckets)
             self.li.search_partial_classes_device(every, q_f16_t, n_buckets, k, part)   # (rows >= nq are padding, never read)
         else:
             self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
         self.dist.all_gather_into_tensor(gathered, part, group=self.group)      # the exchange step of the search proper
         return self.li.merge_partials_device(gathered, self.world, nq, k, out)
+
+    def navigate_sliced(self, q_nav_t, n_buckets):
+        """This rank navigates its slice of the batch; ONE all-gather of [per, n_buckets] int32 blocks rebuilds the
+        bucket lists of all queries (int32 [world * per, n_buckets], rows >= nq are -1 padding)."""
+        import torch
+        nq, dev, W = int(q_nav_t.shape[0]), q_nav_t.device, self.world
+        r = self.dist.get_rank(self.group)
+        per, lo, hi = query_slice_of_rank(nq, r, W)
+        if self._cls is None or self._cls[0].shape != (per, n_buckets):
+            self._cls = (torch.full((per, n_buckets), -1, dtype=torch.int32, device=dev),
+                         torch.empty(W * per, n_buckets, dtype=torch.int32, device=dev))
+        mine, every = self._cls
+        if hi > lo:
+            self.li.navigate_device(q_nav_t[lo:hi], n_buckets, mine)
+        self.dist.all_gather_into_tensor(every, mine, group=self.group)         # bucket lists: nq x n_buckets x 4 bytes
+        return every
 
     def search_host(self, q_nav_host, q_f16_host, n_buckets, k, out_host=None):
         """End-to-end step from (pinned) host tensors that every rank holds: each rank uploads only ITS slice
