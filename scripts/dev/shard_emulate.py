@@ -24,6 +24,8 @@ def main():
     ap.add_argument("--buckets", type=int, default=4)
     ap.add_argument("--rows", type=int, default=10_000_000)
     ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--merge", action="store_true", help="also build every rank's shard, concatenate the partials (the all-gather) "
+                                                         "and time merge_partials_kernel")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "shard_emulate.json"))
     a = ap.parse_args()
     import torch
@@ -63,6 +65,38 @@ def main():
                                  useful_tflops=2 * 768 * st["pairs"] / max(st["ms_rescore_avg"], 1e-6) / 1e9))
                 print(json.dumps(runs[-1]), flush=True)
             li.close()
+    if a.merge:
+        for world in [int(w) for w in a.worlds.split(",")]:
+            parts, keep = [], None
+            fin = []
+            for rank in range(world):
+                li = GpuLearnedIndex(args.categories, rank=rank, world=world,
+                                     shard_policy=SHARD_BUCKETS if a.policy == "buckets" else SHARD_STRIPES)
+                li.set_model(inp["weights"], inp["biases"])
+                li.prepare_device(inp["data_f16"], inp["pred_categories"])
+                p_ = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device=dev)
+                for _ in range(3):
+                    li.search_partial_device(qn, qs, nb, k, p_)
+                torch.cuda.synchronize()
+                fin.append(li.stats()["ms_finalize"])
+                parts.append(p_)
+                if keep is None:
+                    keep = li
+                else:
+                    li.close()
+            gathered = torch.cat(parts)
+            out = (torch.empty(nq, k, dtype=torch.float64, device=dev), torch.empty(nq, k, dtype=torch.int32, device=dev))
+            for _ in range(3):
+                keep.merge_partials_device(gathered, world, nq, k, out)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(a.steps):
+                keep.merge_partials_device(gathered, world, nq, k, out)
+            e1.record(); torch.cuda.synchronize()
+            runs.append(dict(world=world, k=k, merge_ms=e0.elapsed_time(e1) / a.steps, finalize_ms_per_rank=fin,
+                             gathered_mb=gathered.numel() / 1e6))
+            print(json.dumps(runs[-1]), flush=True)
+            keep.close()
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     json.dump(runs, open(a.out, "w"), indent=1)
 
