@@ -213,7 +213,10 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         const WorkItem wi = items[2 * pr];            // both entries of a pair score the same object chunk
         const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
         for (int t = 0; t < n_tiles; ++t) {
-          const int obj0 = wi.obj_begin + t * kTsBlockN + (int)crank * kT2HalfN;
+          int obj0 = wi.obj_begin + t * kTsBlockN + (int)crank * kT2HalfN;
+          // experiment 256: half-pair items re-read a 16-tile window (always an L2 hit) instead of streaming their chunk a
+          // second time -- isolates what the second reader's DRAM traffic costs (results invalid)
+          if (LMI_DBG(dbg_flags, 256) && (wi.flags & kItemHalf)) obj0 = wi.obj_begin + (t & 15) * kTsBlockN + (int)crank * kT2HalfN;
           for (int ks = 0; ks < k_stages; ++ks) {
             const int atoms = min(kTsAtomsPerStage, k_atoms - ks * kTsAtomsPerStage);
             ptx::mbar_wait(ptx::smem_u32(&empty_bar[stage]), phase ^ 1);    // leader's commit, multicast to both CTAs
