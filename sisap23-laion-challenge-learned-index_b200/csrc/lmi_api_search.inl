@@ -19,6 +19,7 @@ class CopyPool {
   static CopyPool& get() { static CopyPool* p = new CopyPool(); return *p; }     // never destroyed: its helpers outlive main()
   void copy(void* dst, const void* src, size_t bytes) {
     if (bytes < ((size_t)1 << 20) || workers_.empty()) { memcpy(dst, src, bytes); return; }
+    std::lock_guard<std::mutex> one_job(call_mu_);          // one copy at a time (indexes on several host threads share the pool)
     std::unique_lock<std::mutex> lk(mu_);
     dst_ = (char*)dst; src_ = (const char*)src; bytes_ = bytes;
     parts_ = (int)workers_.size() + 1;
@@ -53,7 +54,7 @@ class CopyPool {
       drain();
     }
   }
-  std::mutex mu_;
+  std::mutex mu_, call_mu_;
   std::condition_variable cv_, done_;
   std::vector<std::thread> workers_;
   char* dst_ = nullptr; const char* src_ = nullptr; size_t bytes_ = 0;
