@@ -83,7 +83,8 @@ int lmi_create(lmi_index** out, int device, int d_nav, int d, int n_categories);
 void lmi_destroy(lmi_index* idx);
 
 /* name/value tunables: "rescore" (LMI_RESCORE_*), "chunk_objects" (0 = chosen per search), "kprime_extra",
- * "epi_sets" (CTA-pair kernel: epilogue warp sets, 0 = automatic), "timing" (1 = record per-stage CUDA events). */
+ * "epi_sets" (CTA-pair kernel: epilogue warp sets, 0 = automatic), "item_order" (CTA-pair work list: 0 = full pairs
+ * first, 1 = bucket-major), "timing" (1 = record per-stage CUDA events). */
 int lmi_set_option(lmi_index* idx, const char* name, int64_t value);
 
 /* multi-GPU: this index holds shard `rank` of `world`.  Call before lmi_store_begin. */

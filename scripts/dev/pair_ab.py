@@ -107,10 +107,12 @@ def main():
     for f in [int(v) for v in a.dbg.split(",") if v != ""]:
         configs += [(3, 0, f)] if a.dbg_pair_only else [(1, 0, f), (3, 0, f)]
     if a.seq:
-        configs = [tuple(int(v) for v in item.split(":")) for item in a.seq.split(",")]       # rescore:chunk:flags[:epi_sets]
+        configs = [tuple(int(v) for v in item.split(":")) for item in a.seq.split(",")]       # rescore:chunk:flags[:epi_sets[:item_order]]
     for cfg in configs:
         rescore, chunk, flags = cfg[:3]
         sets = cfg[3] if len(cfg) > 3 else 0
+        order = cfg[4] if len(cfg) > 4 else 0
+        li.set_option("item_order", order)
         li.set_option("rescore", rescore)
         li.set_option("chunk_objects", chunk)
         li.set_option("epi_sets", sets)
@@ -132,7 +134,7 @@ def main():
         dd = out[0].cpu().numpy()
         if ref is None:
             ref = (dd, ids)
-        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
+        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, item_order=order, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
                          ms_per_search=ev0.elapsed_time(ev1) / a.steps, k3_ms_avg=st["ms_rescore_avg"],
                          k3_sm_mhz=st["k3_sm_mhz"], work_items=st["n_work_items"], pairs=st["pairs"],
                          padded_pairs=st["padded_pairs"], tile_efficiency=st["pairs"] / max(st["padded_pairs"], 1),

@@ -273,7 +273,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, chunk,
                                         idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
                                         idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>(),
-                                        kernel == LMI_RESCORE_TC_PAIR ? 1 : 0);
+                                        kernel == LMI_RESCORE_TC_PAIR ? (idx->item_order == 1 ? 2 : 1) : 0);
   plan_scatter_kernel<<<C, kScatterThreads, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
                                          idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
   plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());

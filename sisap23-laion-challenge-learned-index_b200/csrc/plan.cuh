@@ -44,10 +44,34 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
                   int64_t* __restrict__ plist_base, WorkItem* __restrict__ items, int max_items,
                   PlanScalars* __restrict__ sc, int pair_mode = 0) {
   __shared__ long long s_scan[1024];
-  __shared__ long long s_carry[3];
+  __shared__ long long s_carry[4];
+  __shared__ long long s_total_full;
   const int tid = threadIdx.x;
-  if (tid < 3) s_carry[tid] = 0;
+  if (tid < 4) s_carry[tid] = 0;
   long long tot_pairs = 0, tot_objs = 0, tot_padded = 0;
+  // Pair mode lists every FULL pair (two 128-row tiles, 1,536 tensor cycles per object tile) before any HALF pair
+  // (an odd last tile split in two, ~half the time per tile): the persistent grid takes entries in list order, and
+  // long items first / short items last packs it better than bucket order (list-scheduling simulation on the bench's
+  // bucket sizes: makespan 1.17 -> 1.10 x ideal on a 1/8 shard, 1.06 -> 1.03 unsharded).  Full pairs of one chunk
+  // stay adjacent (they stream it in lock-step and share it through L2); a half pair runs twice as fast as its
+  // chunk's full pairs and drifts out of their L2 window after a few dozen tiles wherever it is listed.
+  // Pass 1: number of full-pair entries over all buckets = where the half pairs start.
+  {
+    long long my_full = 0;
+    if (pair_mode == 1) {                 // (pair_mode 2 = bucket-major order, kept for A/B runs: option "item_order")
+      for (int b = tid; b < C; b += 1024) {
+        const long long nobj = bucket_ptr[b + 1] - bucket_ptr[b];
+        const long long m = (nobj > 0) ? m_b[b] : 0;
+        const long long ch = (nobj + chunk - 1) / chunk;
+        const long long qt = (m + kTileQ - 1) / kTileQ;
+        my_full += 2 * ch * (qt / 2);
+      }
+    }
+    s_scan[tid] = my_full;
+    __syncthreads();
+    for (int off = 512; off > 0; off >>= 1) { if (tid < off) s_scan[tid] += s_scan[tid + off]; __syncthreads(); }
+    if (tid == 0) s_total_full = s_scan[0];
+  }
   __syncthreads();
   // three running exclusive scans, processed in blocks of 1024 buckets:
   //   0: slots (m_b)   1: items (qtiles*chunks)   2: plists (m_b*chunks)
@@ -80,9 +104,12 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
     //   pairs per chunk; an odd last query tile is split into two half tiles (<= 64 rows each, kItemHalf) of the same chunk
     const long long pairs_per_chunk = pair_mode ? (qt + 1) / 2 : qt / 2;
     const long long n_pair = pair_mode ? ch * pairs_per_chunk : ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
-    long long vals[3] = {m, 2 * n_pair, m * ch};
-    long long excl[3];
-    for (int w = 0; w < 3; ++w) {
+    // scans: 0 slots, 1 entries (pair mode: full-pair entries), 2 partial lists, 3 half-pair entries (pair mode)
+    const long long n_full_e = (pair_mode == 1) ? 2 * ch * (qt / 2) : 2 * n_pair;
+    const long long n_half_e = (pair_mode == 1) ? 2 * ch * (qt & 1) : 0;
+    long long vals[4] = {m, n_full_e, m * ch, n_half_e};
+    long long excl[4];
+    for (int w = 0; w < 4; ++w) {
       s_scan[tid] = vals[w];
       __syncthreads();
       for (int off = 1; off < 1024; off <<= 1) {
@@ -101,6 +128,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
       plist_base[b] = excl[2];
       const long long obj0 = bucket_ptr[b];
       long long it = excl[1];
+      long long it_half = s_total_full + excl[3];
       // order: for every two chunks, their shared pairs first, then the plain pair of their odd
       // tiles -- consecutive items are picked up by clusters that become free one after the other,
       // so everything that streams one chunk runs at about the same time and all but the first
@@ -126,7 +154,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
         ++it;
       };
       // one entry with an explicit row range [row0, row0 + rows) of the bucket's query list
-      auto emit_rows = [&](long long c, long long row0, long long rows, int flags) {
+      auto emit_rows = [&](long long& it, long long c, long long row0, long long rows, int flags) {
         if (it < max_items) {
           WorkItem wi;
           wi.slot_base = (int)excl[0] + (int)row0;
@@ -147,12 +175,13 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
           for (long long p = 0; p < pairs_per_chunk; ++p) {
             const long long r0 = 2 * p * kTileQ;
             if (2 * p + 1 < qt) {
-              emit_rows(c, r0, kTileQ, kItemShared);
-              emit_rows(c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared);
+              emit_rows(it, c, r0, kTileQ, kItemShared);
+              emit_rows(it, c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared);
             } else {                                           // odd last tile: two halves (the second may be empty)
               const long long r = m - r0, h = (r + 1) / 2;
-              emit_rows(c, r0, h, kItemShared | kItemHalf);
-              emit_rows(c, r0 + h, r - h, kItemShared | kItemHalf);
+              long long& ih = (pair_mode == 1) ? it_half : it;
+              emit_rows(ih, c, r0, h, kItemShared | kItemHalf);
+              emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf);
             }
           }
       } else {
@@ -182,7 +211,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
   if (tid == 0) {
     qoff[C] = (int)s_carry[0];
     sc->n_slots = (int)s_carry[0];
-    sc->n_items = (int)min((long long)max_items, s_carry[1]);
+    sc->n_items = (int)min((long long)max_items, s_carry[1] + s_carry[3]);
     sc->n_plists = s_carry[2];
     sc->pairs = pairs;
     sc->bucket_objs = s_scan[0];
