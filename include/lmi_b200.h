@@ -164,6 +164,18 @@ int lmi_search_partial_classes_device(lmi_index* idx, const int32_t* classes_dev
 int lmi_merge_partials_device(lmi_index* idx, const void* gathered_dev, int world, int64_t nq,
                               int k, double* out_dists_dev, uint32_t* out_ids_dev, void* stream);
 
+/* ---- allocation-free navigation --------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  predict_proba on device buffers:
+ * q_nav_dev fp32 [nq, d_nav]; out_classes_dev int64 [nq, n_top] (descending probability, what lmi_navigate returns);
+ * out_probs_dev fp32 [nq, n_top] or NULL; asynchronous on `stream`.  The call allocates nothing: the kernel's int32
+ * bucket lists go to a 4 MiB device array that is part of the library image (held by every GPU that loads the library
+ * until the process exits).  Limit: nq * n_top <= 1,048,576, LMI_ERR_ARG beyond it.  All calls on a device share that
+ * array: calls ordered on one stream are safe, calls that overlap on the GPU race.  The first call on a device resolves
+ * the array's address (cudaGetSymbolAddress): make it before a stream capture begins. */
+int lmi_navigate_device_noalloc(lmi_index* idx, const float* q_nav_dev, int64_t nq, int n_top,
+                                int64_t* out_classes_dev, float* out_probs_dev, void* stream);
+
 /* ---- introspection --------------------------------------------------------------------- */
 int lmi_get_stats(lmi_index* idx, lmi_stats* out);
 /* CSR layout of this shard: bucket_ptr int64 [C+1] (host out). */

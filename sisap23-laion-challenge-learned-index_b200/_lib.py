@@ -18,7 +18,7 @@ SYMBOLS = [
     "lmi_store_end", "lmi_store_save", "lmi_store_load", "lmi_set_buckets",
     "lmi_navigate", "lmi_predict", "lmi_search", "lmi_search_device", "lmi_search_rank",
     "lmi_partial_bytes", "lmi_search_partial_device", "lmi_navigate_device", "lmi_search_partial_classes_device", "lmi_merge_partials_device", "lmi_get_stats",
-    "lmi_get_bucket_ptr", "lmi_rescore_kernel_name",
+    "lmi_get_bucket_ptr", "lmi_rescore_kernel_name", "lmi_navigate_device_noalloc",
 ]
 
 
@@ -80,6 +80,7 @@ def load() -> C.CDLL:
     lib.lmi_navigate_device.argtypes = [p, vp, i64, i, vp, vp]
     lib.lmi_search_partial_classes_device.argtypes = [p, vp, vp, i64, i, i, vp, vp]
     lib.lmi_merge_partials_device.argtypes = [p, vp, i, i64, i, vp, vp, vp]
+    lib.lmi_navigate_device_noalloc.argtypes = [p, vp, i64, i, vp, vp, vp]
     lib.lmi_get_stats.argtypes = [p, C.POINTER(LmiStats)]
     lib.lmi_get_bucket_ptr.argtypes = [p, vp]
     _lib = lib

@@ -214,3 +214,70 @@ int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const flo
 
 #include "lmi_api_store.inl"
 #include "lmi_api_search.inl"
+
+// ---- allocation-free navigation ----------------------------------------------------------------------------------
+// lmi_navigate_device_noalloc (include/lmi_b200.h): predict_proba on device buffers for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  K1 writes its int32 bucket lists into a
+// file-scope device array instead of a grow-only workspace, and a second kernel widens them to the int64 the
+// reference's torch.topk returns.  No counterpart in the reference.
+//
+// The array is part of the library image: every GPU that loads liblmi_b200.so holds its 4 MiB until the process exits.
+// All calls on a device share it, so two calls that overlap on the GPU (different streams, or different indexes on
+// one device) race; calls on one stream are ordered and safe.  Nothing in it has to start at zero: K1 writes every
+// entry [0, nq * n_top) before the widening kernel reads it, so the previous call's contents are never observed.
+namespace lmi {
+
+constexpr int64_t kNoAllocMaxEntries = (int64_t)1 << 20;          // nq * n_top <= 1,048,576 (e.g. 10,000 queries x 100 buckets)
+static __device__ __align__(256) int32_t g_noalloc_classes[kNoAllocMaxEntries];
+
+__global__ void __launch_bounds__(256)
+noalloc_widen_kernel(const int32_t* __restrict__ cls32, int64_t n, int64_t* __restrict__ out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (int64_t)cls32[i];
+}
+
+// In host code `g_noalloc_classes` is only a handle for the runtime, not a device address: the address is asked for
+// once per device, with that device current, and kept.
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static int32_t* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+static int noalloc_scratch(int device, int32_t** out) {
+  if (device < 0 || device >= kNoAllocMaxDevices) return set_error(LMI_ERR_ARG, "device ordinal out of range for the static scratch table");
+  std::lock_guard<std::mutex> g(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    LMI_CUDA(cudaGetSymbolAddress(&p, g_noalloc_classes));          // current device = `device` (set by the caller)
+    if (!p) return set_error(LMI_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[device] = static_cast<int32_t*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return LMI_OK;
+}
+
+}  // namespace lmi
+
+extern "C" int lmi_navigate_device_noalloc(lmi_index* idx, const float* q_nav_dev, int64_t nq, int n_top,
+                                           int64_t* out_classes_dev, float* out_probs_dev, void* stream) {
+  using namespace lmi;
+  if (!idx || !q_nav_dev || !out_classes_dev) return set_error(LMI_ERR_ARG, "NULL argument");
+  if (!idx->has_mlp) return set_error(LMI_ERR_STATE, "Model is not trained, call `build` first.");
+  if (n_top < 1 || n_top > idx->C) return set_error(LMI_ERR_ARG, "n_top must be in [1, n_categories]");
+  if (nq < 0) return set_error(LMI_ERR_ARG, "nq < 0");
+  if (nq > kNoAllocMaxEntries / n_top)
+    return set_error(LMI_ERR_ARG, "lmi_navigate_device_noalloc: nq * n_top = " + std::to_string(nq) + " * " + std::to_string(n_top) +
+                                      " exceeds the static scratch of " + std::to_string(kNoAllocMaxEntries) +
+                                      " entries; split the batch or use lmi_navigate_device");
+  if (nq == 0) return LMI_OK;
+  LMI_CUDA(cudaSetDevice(idx->device));
+  int32_t* scratch = nullptr;
+  int rc = noalloc_scratch(idx->device, &scratch);
+  if (rc != LMI_OK) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  rc = launch_nav(idx, q_nav_dev, nq, n_top, scratch, out_probs_dev, st);
+  if (rc != LMI_OK) return rc;
+  const int64_t n = nq * n_top;
+  noalloc_widen_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(scratch, n, out_classes_dev);
+  LMI_CUDA(cudaGetLastError());
+  return LMI_OK;
+}
