@@ -62,6 +62,8 @@ def parse_args():
                    help="queries checked by oracle.search_intended over the whole dataset (N=1, inside the cpu_baseline leg)")
     p.add_argument("--no-dropin", action="store_true",
                    help="skip the e2e_dropin leg (GpuLearnedIndex.search with a host DataFrame: needs 2 x the dataset in host RAM)")
+    p.add_argument("--no-pipeline", action="store_true",
+                   help="N > 1: issue every step's exchange on the search stream (no overlap with the next step's navigation)")
     p.add_argument("--dbg-flags", type=int, default=0, help="kernel experiments only; results are invalid when non-zero")
     return p.parse_args()
 
@@ -543,8 +545,17 @@ def run_b200(args):
     from lmi_b200.shard import DistributedSearch
     ds = DistributedSearch(li)       # world > 1: partial search -> ONE all-gather (NCCL) -> merge kernel
 
+    # N > 1: the timed loop is a stream of batches, so the exchange step of batch i (all-gather of the partial results +
+    # merge, on a side stream) overlaps navigation / bucket-list all-gather / planning of batch i + 1
+    # (DistributedSearch.search_device_pipelined); every batch's merged result is complete inside the timed region
+    # (flush before the closing event).  --no-pipeline issues everything on one stream.
+    pipelined = world > 1 and not args.no_pipeline
+
     def step():
-        ds.search_device(qn, qs, nb, k, out)
+        if pipelined:
+            ds.search_device_pipelined(qn, qs, nb, k, out)
+        else:
+            ds.search_device(qn, qs, nb, k, out)
 
     def barrier():
         if world > 1:
@@ -553,7 +564,14 @@ def run_b200(args):
 
     for _ in range(max(args.warmup, 3)):
         step()
+    ds.flush_pipelined()
     barrier()
+    if pipelined:                    # same batch through the one-stream path: the overlapped exchange must not change a bit
+        out_ref = (torch.empty_like(out[0]), torch.empty_like(out[1]))
+        ds.search_device(qn, qs, nb, k, out_ref)
+        torch.cuda.synchronize()
+        assert torch.equal(out_ref[1], out[1]) and torch.equal(out_ref[0], out[0]), "pipelined exchange changed the result"
+        del out_ref
     li.stats()                       # consume the warm-up's kernel timings
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -563,6 +581,7 @@ def run_b200(args):
     ev0.record()
     for _ in range(args.steps):
         step()
+    ds.flush_pipelined()             # the search stream waits for the last exchanges: all K results are inside the region
     ev1.record()
     barrier()
     clocks = sampler.stop()
@@ -584,6 +603,8 @@ def run_b200(args):
         step()
         s_ = li.stats()
         rescore_ms_isolated.append(s_["ms_rescore"]); mhz_isolated.append(s_["k3_sm_mhz"])
+    ds.flush_pipelined()
+    torch.cuda.synchronize()
     # SM clock the kernel itself saw (clock64 / globaltimer inside the kernel): last timed step vs launched alone
     clocks["sm_mhz_in_kernel"] = st_loop["k3_sm_mhz"]
     clocks["sm_mhz_in_kernel_isolated"] = float(np.mean(mhz_isolated))
@@ -796,6 +817,8 @@ def run_b200(args):
                                    f"n_buckets={nb}, nq={nq}, k={k} (BASELINE.json configs[1] when defaults)",
                        "l2": "inputs larger than L2 (15.4 GB bucket store streamed every step)",
                        "shard": args.shard if world > 1 else "none", "rescore": args.rescore,
+                       "pipeline": ("exchange of batch i (all-gather + merge, side stream) overlaps navigation and planning "
+                                    "of batch i+1; all K merged results complete inside the timed region") if pipelined else "none",
                        "synthetic": {"blobs": args.blobs, "sigma": args.sigma}},
             "e2e": e2e, "e2e_dropin": dropin, "gpu_launches": args.steps * (8 + (1 if world > 1 else 0)),   # nav, 4 plan kernels, rescoring, finalize, exact fallback (+ merge)
             "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,

@@ -19,8 +19,9 @@
 namespace lmi {
 
 constexpr int kFinWarps = 8;
-constexpr int kFinRegE = 24;          // entries per lane of the register-resident selection (<= 768 entries per query)
-constexpr int kFinRegBig = 48;        // same for the bisection selection used when k' >= 64 (<= 1536 entries per query)
+constexpr int kFinRegSmall = 8;      // entries per lane of the register-resident selection: <= 256 entries per query,
+constexpr int kFinRegE = 24;          // <= 768,
+constexpr int kFinRegBig = 48;        // <= 1536 (k' >= 64 instantiation only)
 constexpr int kFinMaxVec = 128;       // uint4 per row, d <= 1024
 constexpr double kCertEps = 2e-5;       // bound used by the exactness certificate
 
@@ -162,7 +163,10 @@ __device__ __forceinline__ int fin_select_bisect(int lane, int R, int total, con
 }
 
 // mode 0: write out_dists/out_ids [nq,k];  mode 1: write Partial [nq,k]
-__global__ void __launch_bounds__(kFinWarps * 32)
+// kBig: instantiation for k' >= 64 (up to 48 register-resident entries per lane in the selection); the k' <= 32
+// instantiation stops at 24 entries per lane and is compiled for three CTAs per SM.
+template <bool kBig>
+__global__ void __launch_bounds__(kFinWarps * 32, kBig ? 2 : 4)
 finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
                 const int32_t* __restrict__ top_cls, const int32_t* __restrict__ pair_slot,
                 const int32_t* __restrict__ qoff, const int32_t* __restrict__ chunks_b,
@@ -172,10 +176,11 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
                 PlanScalars* __restrict__ sc, int32_t* __restrict__ uncert_list, int mode,
                 double* __restrict__ out_dists, uint32_t* __restrict__ out_ids,
                 Partial* __restrict__ out_partial) {
-  __shared__ int32_t s_pos[kFinWarps][kMaxKPrime];
-  __shared__ uint32_t s_rank[kFinWarps][kMaxKPrime];
-  __shared__ uint32_t s_id[kFinWarps][kMaxKPrime];
-  __shared__ double s_dist[kFinWarps][kMaxKPrime];
+  constexpr int kSel = kBig ? kMaxKPrime : 32;  // survivors per query (R = k')
+  __shared__ int32_t s_pos[kFinWarps][kSel];
+  __shared__ uint32_t s_rank[kFinWarps][kSel];
+  __shared__ uint32_t s_id[kFinWarps][kSel];
+  __shared__ double s_dist[kFinWarps][kSel];
   __shared__ int64_t s_rbeg[kFinWarps][32];     // per rank: first entry (global Cand index)
   __shared__ int32_t s_rcum[kFinWarps][33];     // per rank: cumulative entry count
   __shared__ uint4 s_q[kFinWarps][kFinMaxVec];  // the query row (fp16 bits)
@@ -217,60 +222,28 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
     __syncwarp();
   };
 
-  // Fast path (the usual case: one rank group and at most 32 x kFinRegE entries, e.g. 4 ranks x 3 chunks
-  // x k' = 16): every lane reads its entries once and the R rounds run on registers.
-  bool fast = (n_groups == 1);
-  bool bisect = false;
-  float score_R_sel = 0.f;                             // R-th best fp32 score (set by whichever selection ran)
-  if (fast) {
+  // Usual case (one rank group, entries fit the registers of a warp -- e.g. 4 ranks x 3 chunks x k' = 16 = 192
+  // entries, 6 per lane): every lane reads its entries once and the R best are found by bisection on the score
+  // (32 steps of NE compares + one warp reduction; R rounds of warp arg-max over NE entries -- the round-1 form --
+  // were 45 % of this kernel's instructions at k' = 16).  NE is the smallest of 8 / 24 / 48 that holds the entries.
+  int sel_ne = 0;                                      // 0: general path below
+  float score_R_sel = 0.f;                             // R-th best fp32 score (bisection paths)
+  if (n_groups == 1) {
     load_ranges(0);
-    bisect = R >= 64 && s_rcum[warp][nb] <= 32 * kFinRegBig;
-    fast = !bisect && s_rcum[warp][nb] <= 32 * kFinRegE;
+    const int total = s_rcum[warp][nb];
+    if (total <= 32 * kFinRegSmall) sel_ne = kFinRegSmall;
+    else if (total <= 32 * kFinRegE) sel_ne = kFinRegE;
+    else if (kBig && total <= 32 * kFinRegBig) sel_ne = kFinRegBig;
   }
-  if (bisect) {
+  if (sel_ne == kFinRegSmall) {
+    n_sel = fin_select_bisect<kFinRegSmall>(lane, R, s_rcum[warp][nb], s_rcum[warp], s_rbeg[warp], plists,
+                                            s_pos[warp], s_rank[warp], s_dist[warp], score_R_sel);
+  } else if (sel_ne == kFinRegE) {
+    n_sel = fin_select_bisect<kFinRegE>(lane, R, s_rcum[warp][nb], s_rcum[warp], s_rbeg[warp], plists,
+                                        s_pos[warp], s_rank[warp], s_dist[warp], score_R_sel);
+  } else if (kBig && sel_ne == kFinRegBig) {
     n_sel = fin_select_bisect<kFinRegBig>(lane, R, s_rcum[warp][nb], s_rcum[warp], s_rbeg[warp], plists,
                                           s_pos[warp], s_rank[warp], s_dist[warp], score_R_sel);
-  } else if (fast) {
-    const int total = s_rcum[warp][nb];
-    float es[kFinRegE]; int32_t ep[kFinRegE];
-#pragma unroll
-    for (int u = 0; u < kFinRegE; ++u) {
-      const int g = lane + 32 * u;                 // entry number in (rank, list, position) order
-      es[u] = kNegInf * 2.f; ep[u] = -1;
-      if (g < total) {
-        int r = 0;
-        while (g >= s_rcum[warp][r + 1]) ++r;
-        const Cand c = plists[s_rbeg[warp][r] + (g - s_rcum[warp][r])];
-        if (c.pos >= 0) { es[u] = c.score; ep[u] = c.pos; }
-      }
-    }
-    for (int t = 0; t < R; ++t) {
-      // per lane: best remaining entry with its payload (select chains only: the arrays stay in registers)
-      float best_s = kNegInf * 2.f; int best_g = 0x7fffffff; int32_t best_p = -1;
-#pragma unroll
-      for (int u = 0; u < kFinRegE; ++u) {         // ascending g per lane: strict '>' keeps the lowest g of equal scores
-        const bool better = ep[u] >= 0 && es[u] > best_s;
-        best_s = better ? es[u] : best_s;
-        best_g = better ? lane + 32 * u : best_g;
-        best_p = better ? ep[u] : best_p;
-      }
-      float win_s = best_s; int win_g = best_g;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float os = __shfl_xor_sync(0xffffffffu, win_s, o);
-        const int og = __shfl_xor_sync(0xffffffffu, win_g, o);
-        if (os > win_s || (os == win_s && og < win_g)) { win_s = os; win_g = og; }
-      }
-      if (win_g == 0x7fffffff) break;              // no more valid entries (warp-uniform)
-      if (win_g == best_g) {                       // exactly one lane
-        int r = 0;                                 // bucket rank of the entry: the range it falls in
-        while (win_g >= s_rcum[warp][r + 1]) ++r;
-        s_pos[warp][t] = best_p; s_rank[warp][t] = (uint32_t)r; s_dist[warp][t] = (double)best_s;
-      }
-#pragma unroll
-      for (int u = 0; u < kFinRegE; ++u) ep[u] = (lane + 32 * u == win_g) ? -1 : ep[u];     // taken
-      n_sel = t + 1;
-    }
   } else {
   for (int t = 0; t < R; ++t) {
       float best_s = kNegInf * 2.f;      // -inf
@@ -338,7 +311,7 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   const double qn = fin_load_query(qrow, sq, vec, lane);
   double max_err = 0.0;
   // (the round-based selections leave the scores in descending order; read before they are overwritten)
-  const float score_R = (n_sel == R) ? (bisect ? score_R_sel : (float)s_dist[warp][R - 1]) : 0.f;
+  const float score_R = (n_sel == R) ? (sel_ne != 0 ? score_R_sel : (float)s_dist[warp][R - 1]) : 0.f;
   __syncwarp();
   const int grp = lane >> 3, sub = lane & 7;
   for (int t0 = 0; t0 < n_sel; t0 += 4) {

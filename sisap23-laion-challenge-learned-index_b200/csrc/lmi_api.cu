@@ -191,9 +191,11 @@ int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const flo
     if (out <= 0 || out > 65536) return set_error(LMI_ERR_ARG, "layer width out of range");
     L.in_dim[l] = in; L.out_dim[l] = out;
     L.max_width = std::max(L.max_width, out);
-    std::vector<float> wt((size_t)in * out);            // transpose nn.Linear.weight [out,in] -> [in,out]
+    const int pitch = (out + 3) & ~3;                   // rows padded with zeros to a multiple of 4 floats (16-byte loads)
+    L.pitch[l] = pitch;
+    std::vector<float> wt((size_t)in * pitch, 0.f);     // transpose nn.Linear.weight [out,in] -> [in,pitch]
     for (int o = 0; o < out; ++o)
-      for (int i = 0; i < in; ++i) wt[(size_t)i * out + o] = W[l][(size_t)o * in + i];
+      for (int i = 0; i < in; ++i) wt[(size_t)i * pitch + o] = W[l][(size_t)o * in + i];
     float *dw = nullptr, *db = nullptr;
     LMI_CUDA(cudaMalloc(&dw, wt.size() * sizeof(float)));
     idx->mlp_allocs.push_back(dw);
@@ -204,6 +206,13 @@ int lmi_set_mlp(lmi_index* idx, int n_layers, const int32_t* out_dims, const flo
     L.wt[l] = dw; L.bias[l] = db;
     in = out;
   }
+  // activation ping-pong: buffer A holds the input and the outputs of layers 1, 3, ...; buffer B those of layers 0, 2, ...
+  L.width_a = idx->d_nav; L.width_b = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    int& w = (l & 1) ? L.width_a : L.width_b;
+    w = std::max(w, L.out_dim[l]);
+  }
+  L.width_a = (L.width_a + 3) & ~3; L.width_b = (L.width_b + 3) & ~3;
   if (nav_smem_bytes(L) > 200 * 1024) return set_error(LMI_ERR_ARG, "MLP too wide for the navigation kernel (max width 800)");
   idx->layers = L;
   idx->has_mlp = true;            // (the shared-memory opt-in of nav_kernel is set at every launch: launch_nav)

@@ -297,7 +297,8 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   if (rc != LMI_OK) return rc;
   if (timing) { LMI_CUDA(cudaEventRecord(ring[1], st)); LMI_CUDA(cudaEventRecord(idx->ev[3], st)); ++idx->n_since_stats; }
   // ---- K4 + K5 finalize ----
-  finalize_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, st>>>(
+  auto fin = (KP >= 64) ? finalize_kernel<true> : finalize_kernel<false>;
+  fin<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, st>>>(
       nq, nb, k, KP, d, top, idx->pair_slot.as<int32_t>(), idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(),
       idx->plist_base.as<int64_t>(), idx->plists.as<Cand>(), q16_dev, idx->x, idx->ids, thr_dev,
       idx->scalars.as<PlanScalars>(), idx->uncert.as<int32_t>(), mode, out_d, out_i, out_p);

@@ -7,14 +7,15 @@
 //
 // One CTA = 16 queries (128 threads).  Activations live in shared memory transposed ([feature][query]) so a
 // thread that owns 8 queries x 4 outputs reads its 8 activations with two broadcast LDS.128;
-// weights are stored transposed on the device ([in][out]) and streamed through shared memory in
-// tiles of 8 input rows x 256 outputs, the next tile's loads in flight while one is consumed.
+// weights are stored transposed on the device ([in][out], rows padded to a multiple of 4 floats) and streamed
+// through shared memory in tiles of 8 input rows x 256 outputs with 16-byte loads, the next tile's loads in flight
+// while one is consumed.
 #pragma once
 #include "common.cuh"
 
 namespace lmi {
 
-constexpr int kNavTQ = 16;          // queries per CTA (10k queries = 625 CTAs, 4 per SM: small CTAs balance the 148 SMs)
+constexpr int kNavTQ = 16;          // queries per CTA (10k queries = 625 CTAs, 5 per SM: all resident at once)
 constexpr int kNavThreads = 128;
 constexpr int kNavMaxLayers = 8;
 constexpr int kNavKT = 8;           // input rows per weight tile
@@ -25,9 +26,11 @@ struct NavLayers {
   int n_layers;
   int in_dim[kNavMaxLayers];
   int out_dim[kNavMaxLayers];
-  const float* wt[kNavMaxLayers];    // [in][out]  (transposed nn.Linear.weight)
+  int pitch[kNavMaxLayers];          // floats per row of wt: out_dim rounded up to a multiple of 4, zero-filled (16-byte loads)
+  const float* wt[kNavMaxLayers];    // [in][pitch]  (transposed nn.Linear.weight)
   const float* bias[kNavMaxLayers];  // [out]
   int max_width;                     // max over all in/out dims
+  int width_a, width_b;              // activation buffers: A holds the input and every second layer's output, B the others
 };
 
 // One weight tile (rows x 256 outputs in shared memory) into a thread's 8 queries x NU*1 outputs.
@@ -53,12 +56,12 @@ __device__ __forceinline__ void nav_tile_fma(float (&acc)[4][8], const float* __
 }
 
 // x: [n, d_nav] fp32.  out_classes: int32 [n, n_top]; out_probs: fp32 [n, n_top] or nullptr.
-__global__ void __launch_bounds__(kNavThreads, 4)
+__global__ void __launch_bounds__(kNavThreads, 5)
 nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
            int32_t* __restrict__ out_classes, float* __restrict__ out_probs) {
   extern __shared__ float nav_smem[];
   float* act_a = nav_smem;
-  float* act_b = nav_smem + (size_t)L.max_width * kNavTQ;
+  float* act_b = nav_smem + (size_t)L.width_a * kNavTQ;
   const int tid = threadIdx.x;
   const int64_t q0 = (int64_t)blockIdx.x * kNavTQ;
   const int nq_here = (int)min((int64_t)kNavTQ, n - q0);
@@ -80,7 +83,7 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
   const int qg = tid >> 6;           // query group: queries qg*8 .. qg*8+7
   float* cur = act_a;
   float* nxt = act_b;
-  float* wtile = nav_smem + (size_t)2 * L.max_width * kNavTQ;       // [2][kNavKT][kNavOB]
+  float* wtile = nav_smem + (size_t)(L.width_a + L.width_b) * kNavTQ;   // [2][kNavKT][kNavOB]
   for (int l = 0; l < L.n_layers; ++l) {
     const int I = L.in_dim[l], O = L.out_dim[l];
     const float* __restrict__ wt = L.wt[l];
@@ -98,24 +101,25 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[u][j] = bv;
       }
-      constexpr int kCols = kNavOB / kNavThreads;          // tile columns per thread
-      float wreg[kNavKT][kCols];
-      auto fetch = [&](int t) {              // a row of the tile is kNavOB consecutive floats: coalesced
+      // a tile is kNavKT rows x 64 float4: thread `tid` moves column tid & 63 of rows (tid >> 6) + 2j, j = 0..3, with
+      // 16-byte loads and stores (rows of wt are padded to a multiple of 4 floats with zeros)
+      constexpr int kVec = kNavKT * (kNavOB / 4) / kNavThreads;          // float4 per thread and tile
+      const int P = L.pitch[l];
+      const int c4 = (tid & 63) * 4;
+      const bool col_ok = ob + c4 < P;
+      const float* __restrict__ wcol = wt + ob + c4;
+      float4 wreg[kVec];
+      auto fetch = [&](int t) {
 #pragma unroll
-        for (int r = 0; r < kNavKT; ++r) {
-          const int i = t * kNavKT + r;
-#pragma unroll
-          for (int cc = 0; cc < kCols; ++cc) {
-            const int c = tid + cc * kNavThreads;
-            wreg[r][cc] = (i < I && c < ncols) ? __ldg(wt + (size_t)i * O + ob + c) : 0.f;
-          }
+        for (int j = 0; j < kVec; ++j) {
+          const int i = t * kNavKT + (tid >> 6) + 2 * j;
+          wreg[j] = (col_ok && i < I) ? __ldg(reinterpret_cast<const float4*>(wcol + (size_t)i * P)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
       auto stash = [&](int buf) {
 #pragma unroll
-        for (int r = 0; r < kNavKT; ++r)
-#pragma unroll
-          for (int cc = 0; cc < kCols; ++cc) wtile[(buf * kNavKT + r) * kNavOB + tid + cc * kNavThreads] = wreg[r][cc];
+        for (int j = 0; j < kVec; ++j)
+          *reinterpret_cast<float4*>(wtile + (buf * kNavKT + (tid >> 6) + 2 * j) * kNavOB + c4) = wreg[j];
       };
       fetch(0);
       stash(0);
@@ -231,7 +235,7 @@ nav_kernel(const float* __restrict__ x, int64_t n, NavLayers L, int n_top,
 }
 
 inline size_t nav_smem_bytes(const NavLayers& L) {
-  return ((size_t)2 * L.max_width * kNavTQ + (size_t)2 * kNavKT * kNavOB) * sizeof(float);
+  return ((size_t)(L.width_a + L.width_b) * kNavTQ + (size_t)2 * kNavKT * kNavOB) * sizeof(float);
 }
 
 }  // namespace lmi

@@ -118,6 +118,12 @@ class DistributedSearch:
         self.slice_navigation = slice_navigation
         self._bufs = None
         self._cls = None
+        # search_device_pipelined: exchange stream, its own communicator, two sets of exchange buffers
+        self._xs = None
+        self._xgroup = None
+        self._ring = None
+        self._ring_done = [None, None]
+        self._n_pipelined = 0
 
     def search_device(self, q_nav_t, q_f16_t, n_buckets, k, out=None):
         import torch
@@ -139,6 +145,64 @@ class DistributedSearch:
             self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
         self.dist.all_gather_into_tensor(gathered, part, group=self.group)      # the exchange step of the search proper
         return self.li.merge_partials_device(gathered, self.world, nq, k, out)
+
+    def search_device_pipelined(self, q_nav_t, q_f16_t, n_buckets, k, out):
+        """Throughput form of ``search_device`` for a stream of batches: the exchange step of batch i (all-gather of the
+        partial results + merge kernel) runs on a side stream while the caller's stream goes on to batch i + 1, whose
+        navigation, bucket-list all-gather and planning use the GPU only lightly.  Per-rank results, merge key and
+        therefore the output are those of ``search_device``; only the stream the merge runs on differs.
+
+        Returns a ``torch.cuda.Event`` recorded behind the merge: ``out`` may be read once it has completed
+        (``event.wait()`` makes the current stream wait for it, ``event.synchronize()`` the host).  The partial and
+        gathered buffers are double-buffered; a third call waits for the first one's exchange.  The exchange uses its
+        own NCCL communicator (created collectively on the first call) so that it does not queue behind, or ahead of,
+        the next batch's bucket-list all-gather on one NCCL stream.  Every rank must issue the same calls in the same
+        order, as with any collective."""
+        import torch
+        nq = int(q_f16_t.shape[0])
+        dev = q_f16_t.device
+        if self.world == 1:
+            self.li.search_device(q_nav_t, q_f16_t, n_buckets, k, out)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            return ev
+        if self._xs is None:
+            self._xs = torch.cuda.Stream(device=dev)
+            ranks = None if self.group is None else self.dist.get_process_group_ranks(self.group)
+            self._xgroup = self.dist.new_group(ranks=ranks)
+        nbytes = self.li.partial_bytes(nq, k)
+        if self._ring is None or self._ring[0][0].numel() != nbytes:
+            self.flush_pipelined()
+            self._ring = [(torch.empty(nbytes, dtype=torch.uint8, device=dev),
+                           torch.empty(self.world * nbytes, dtype=torch.uint8, device=dev)) for _ in range(2)]
+            self._ring_done = [None, None]
+        slot = self._n_pipelined & 1
+        self._n_pipelined += 1
+        part, gathered = self._ring[slot]
+        main = torch.cuda.current_stream(dev)
+        if self._ring_done[slot] is not None:
+            main.wait_event(self._ring_done[slot])           # the exchange two batches back has read `part`
+        if self.slice_navigation:
+            every = self.navigate_sliced(q_nav_t, n_buckets)
+            self.li.search_partial_classes_device(every, q_f16_t, n_buckets, k, part)
+        else:
+            self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        done = torch.cuda.Event()
+        with torch.cuda.stream(self._xs):
+            self._xs.wait_event(ready)
+            self.dist.all_gather_into_tensor(gathered, part, group=self._xgroup)
+            self.li.merge_partials_device(gathered, self.world, nq, k, out)
+            done.record(self._xs)
+        self._ring_done[slot] = done
+        return done
+
+    def flush_pipelined(self):
+        """The current stream waits for every exchange issued by ``search_device_pipelined``."""
+        for ev in self._ring_done:
+            if ev is not None:
+                ev.wait()
 
     def navigate_sliced(self, q_nav_t, n_buckets):
         """This rank navigates its slice of the batch; ONE all-gather of [per, n_buckets] int32 blocks rebuilds the
