@@ -62,6 +62,8 @@ def parse_args():
                    help="queries checked by oracle.search_intended over the whole dataset (N=1, inside the cpu_baseline leg)")
     p.add_argument("--no-dropin", action="store_true",
                    help="skip the e2e_dropin leg (GpuLearnedIndex.search with a host DataFrame: needs 2 x the dataset in host RAM)")
+    p.add_argument("--nav-mode", choices=["sliced", "replicated"], default="sliced",
+                   help="N > 1: every rank navigates 1/N of the batch + all-gather of the bucket lists, or all of it (no collective)")
     p.add_argument("--no-pipeline", action="store_true",
                    help="N > 1: issue every step's exchange on the search stream (no overlap with the next step's navigation)")
     p.add_argument("--dbg-flags", type=int, default=0, help="kernel experiments only; results are invalid when non-zero")
@@ -543,7 +545,7 @@ def run_b200(args):
     qn, qs = inp["queries_nav"].contiguous(), inp["queries_f16"].contiguous()
     out = (torch.empty(nq, k, dtype=torch.float64, device=device), torch.empty(nq, k, dtype=torch.int32, device=device))
     from lmi_b200.shard import DistributedSearch
-    ds = DistributedSearch(li)       # world > 1: partial search -> ONE all-gather (NCCL) -> merge kernel
+    ds = DistributedSearch(li, slice_navigation=(args.nav_mode == "sliced"))   # world > 1: partial search -> ONE all-gather (NCCL) -> merge kernel
 
     # N > 1: the timed loop is a stream of batches, so the exchange step of batch i (all-gather of the partial results +
     # merge, on a side stream) overlaps navigation / bucket-list all-gather / planning of batch i + 1
@@ -817,6 +819,7 @@ def run_b200(args):
                                    f"n_buckets={nb}, nq={nq}, k={k} (BASELINE.json configs[1] when defaults)",
                        "l2": "inputs larger than L2 (15.4 GB bucket store streamed every step)",
                        "shard": args.shard if world > 1 else "none", "rescore": args.rescore,
+                       "navigation": args.nav_mode if world > 1 else "local",
                        "pipeline": ("exchange of batch i (all-gather + merge, side stream) overlaps navigation and planning "
                                     "of batch i+1; all K merged results complete inside the timed region") if pipelined else "none",
                        "synthetic": {"blobs": args.blobs, "sigma": args.sigma}},
