@@ -496,8 +496,12 @@ exact_fixup_kernel(int64_t nq, int nb, int k, int d, const int32_t* __restrict__
 // Multi-GPU: k best of world*k gathered entries per query.  One warp per query: the entries are staged in
 // shared memory (up to kMergeSmemE per query) and every lane ranks its own entries against all of them
 // (broadcast reads); larger inputs (world * k > kMergeSmemE) rank straight from global memory.
+// kSmall: instantiation for world * k <= kMergeSmemE (k = 10 on up to 12 ranks): only the shared-memory path, few
+// registers, so every CTA of a 10k-query batch is resident at once -- the merge runs beside the next batch's navigation
+// on the exchange stream and should be gone before that batch's rescoring kernel wants every SM.
 constexpr int kMergeSmemE = 128;
-__global__ void __launch_bounds__(kFinWarps * 32)
+template <bool kSmall>
+__global__ void __launch_bounds__(kFinWarps * 32, kSmall ? 8 : 2)
 merge_partials_kernel(const Partial* __restrict__ gathered, int world, int64_t nq, int k,
                       double* __restrict__ out_dists, uint32_t* __restrict__ out_ids) {
   __shared__ Partial s_e[kFinWarps][kMergeSmemE];
@@ -505,14 +509,26 @@ merge_partials_kernel(const Partial* __restrict__ gathered, int world, int64_t n
   const int64_t qi = (int64_t)blockIdx.x * kFinWarps + warp;
   if (qi >= nq) return;
   const int E = world * k;
-  if (E <= kMergeSmemE) {
-    for (int t = lane; t < E; t += 32) {
-      const int w = t / k;
-      s_e[warp][t] = gathered[((int64_t)w * nq + qi) * k + (t - w * k)];
+  if (kSmall || E <= kMergeSmemE) {
+    int n_valid = 0;
+    for (int t0 = 0; t0 < E; t0 += 32) {
+      const int t = t0 + lane;
+      bool valid = false;
+      if (t < E) {
+        const int w = t / k;
+        const Partial p = gathered[((int64_t)w * nq + qi) * k + (t - w * k)];
+        s_e[warp][t] = p;
+        valid = p.dist != kEmptyDist;
+      }
+      n_valid += __popc(__ballot_sync(0xffffffffu, valid));
     }
     __syncwarp();
+    // empty slots (10000.0, id 0) sort behind every real entry: when k real entries exist they are not ranked at all
+    // (on a bucket shard at most n_buckets of the `world` lists of a query hold anything)
+    const bool skip_empty = n_valid >= k;
     for (int t = lane; t < E; t += 32) {
       const Partial pt = s_e[warp][t];
+      if (skip_empty && pt.dist == kEmptyDist) continue;
       int ord = 0;
       for (int u = 0; u < E; ++u) {
         const Partial pu = s_e[warp][u];
@@ -522,6 +538,7 @@ merge_partials_kernel(const Partial* __restrict__ gathered, int world, int64_t n
     }
     return;
   }
+  if (kSmall) return;                              // (not reached: the host picks this instantiation by world * k)
   // Large inputs (k = 100 on 8 ranks: 800 entries).  Up to 1,024 entries: every lane keeps the distance bits of its
   // <= 32 entries in registers, a bisection over the differing bits finds the k-th smallest distance (non-negative
   // doubles order like their bit patterns), one ballot pass compacts the k survivors into shared memory and they

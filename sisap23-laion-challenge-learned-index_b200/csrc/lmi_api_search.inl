@@ -475,7 +475,8 @@ int lmi_merge_partials_device(lmi_index* idx, const void* gathered_dev, int worl
   if (!idx || !gathered_dev || !out_dists_dev || !out_ids_dev) return set_error(LMI_ERR_ARG, "NULL argument");
   if (world < 1 || nq <= 0 || k < 1) return set_error(LMI_ERR_ARG, "bad world/nq/k");
   LMI_CUDA(cudaSetDevice(idx->device));
-  merge_partials_kernel<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  auto merge = ((int64_t)world * k <= kMergeSmemE) ? merge_partials_kernel<true> : merge_partials_kernel<false>;
+  merge<<<(unsigned)((nq + kFinWarps - 1) / kFinWarps), kFinWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const Partial*>(gathered_dev), world, nq, k, out_dists_dev, out_ids_dev);
   LMI_CUDA(cudaGetLastError());
   return LMI_OK;
