@@ -147,7 +147,7 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
     idx->kprime_extra = (int)value;
   } else if (n == "item_order") {
-    if (value < 0 || value > 1) return set_error(LMI_ERR_ARG, "item_order: 0 (full pairs first) or 1 (bucket-major)");
+    if (value < 0 || value > 2) return set_error(LMI_ERR_ARG, "item_order: 0 (full pairs first), 1 (bucket-major) or 2 (0 + three-tile buckets as three half pairs)");
     idx->item_order = (int)value;
   } else if (n == "epi_sets") {
     if (value < 0 || value > 2) return set_error(LMI_ERR_ARG, "epi_sets: 0 (automatic), 1 or 2 epilogue warp sets in the CTA-pair kernel");

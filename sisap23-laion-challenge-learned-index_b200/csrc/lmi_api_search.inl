@@ -223,8 +223,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   }
   // entries: at most qtiles_b * chunks_b + 1 (dummy) per bucket
   // (pair mode of the CTA-pair kernel: an odd last tile becomes two entries -> one more per bucket and chunk)
-  const int64_t items_a = (qtiles_max + 1) * total_chunks + C;
-  const int64_t items_b = (n_pairs / kTileQ + 2 * C) * std::max<int64_t>(max_chunks, 1) + C;
+  // (item_order 2 lists a three-tile bucket as three half pairs: up to 2 entries per tile)
+  const int64_t items_a = (2 * qtiles_max + 1) * total_chunks + C;
+  const int64_t items_b = (2 * n_pairs / kTileQ + 2 * C) * std::max<int64_t>(max_chunks, 1) + C;
   const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
   if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
@@ -273,7 +274,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, chunk,
                                         idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
                                         idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>(),
-                                        kernel == LMI_RESCORE_TC_PAIR ? (idx->item_order == 1 ? 2 : 1) : 0);
+                                        kernel == LMI_RESCORE_TC_PAIR ? (idx->item_order == 1 ? 2 : idx->item_order == 2 ? 3 : 1) : 0);
   plan_scatter_kernel<<<C, kScatterThreads, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
                                          idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
   plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());

@@ -58,13 +58,13 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
   // Pass 1: number of full-pair entries over all buckets = where the half pairs start.
   {
     long long my_full = 0;
-    if (pair_mode == 1) {                 // (pair_mode 2 = bucket-major order, kept for A/B runs: option "item_order")
+    if (pair_mode == 1 || pair_mode == 3) {   // (pair_mode 2 = bucket-major order, kept for A/B runs: option "item_order")
       for (int b = tid; b < C; b += 1024) {
         const long long nobj = bucket_ptr[b + 1] - bucket_ptr[b];
         const long long m = (nobj > 0) ? m_b[b] : 0;
         const long long ch = (nobj + chunk - 1) / chunk;
         const long long qt = (m + kTileQ - 1) / kTileQ;
-        my_full += 2 * ch * (qt / 2);
+        if (!(pair_mode == 3 && qt == 3)) my_full += 2 * ch * (qt / 2);
       }
     }
     s_scan[tid] = my_full;
@@ -105,8 +105,13 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
     const long long pairs_per_chunk = pair_mode ? (qt + 1) / 2 : qt / 2;
     const long long n_pair = pair_mode ? ch * pairs_per_chunk : ch * pairs_per_chunk + ((qt & 1) ? (ch + 1) / 2 : 0);
     // scans: 0 slots, 1 entries (pair mode: full-pair entries), 2 partial lists, 3 half-pair entries (pair mode)
-    const long long n_full_e = (pair_mode == 1) ? 2 * ch * (qt / 2) : 2 * n_pair;
-    const long long n_half_e = (pair_mode == 1) ? 2 * ch * (qt & 1) : 0;
+    // pair_mode 3 (experiment, option item_order = 2): as 1, but a bucket with exactly three query tiles runs as THREE half
+    // pairs per chunk (all M = 128 MMAs, equal speed, adjacent in the list -> one DRAM read of the chunk shared through L2)
+    // instead of one full pair + one half pair that run at 1 : 2 and read the chunk twice
+    const bool all_half = (pair_mode == 3 && qt == 3);
+    const bool split_order = (pair_mode == 1 || pair_mode == 3);
+    const long long n_full_e = all_half ? 0 : split_order ? 2 * ch * (qt / 2) : 2 * n_pair;
+    const long long n_half_e = all_half ? 2 * ch * qt : split_order ? 2 * ch * (qt & 1) : 0;
     long long vals[4] = {m, n_full_e, m * ch, n_half_e};
     long long excl[4];
     for (int w = 0; w < 4; ++w) {
@@ -170,7 +175,14 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
         }
         ++it;
       };
-      if (pair_mode) {
+      if (all_half) {
+        for (long long c = 0; c < ch; ++c)
+          for (long long t = 0; t < qt; ++t) {
+            const long long r0 = t * kTileQ, r = min((long long)kTileQ, m - r0), h = (r + 1) / 2;
+            emit_rows(it_half, c, r0, h, kItemShared | kItemHalf);
+            emit_rows(it_half, c, r0 + h, r - h, kItemShared | kItemHalf);
+          }
+      } else if (pair_mode) {
         for (long long c = 0; c < ch; ++c)
           for (long long p = 0; p < pairs_per_chunk; ++p) {
             const long long r0 = 2 * p * kTileQ;
@@ -179,7 +191,7 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
               emit_rows(it, c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared);
             } else {                                           // odd last tile: two halves (the second may be empty)
               const long long r = m - r0, h = (r + 1) / 2;
-              long long& ih = (pair_mode == 1) ? it_half : it;
+              long long& ih = split_order ? it_half : it;
               emit_rows(ih, c, r0, h, kItemShared | kItemHalf);
               emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf);
             }
