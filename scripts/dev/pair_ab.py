@@ -72,6 +72,7 @@ def main():
                                               "interleave variants -- the power-capped clock drifts over a process lifetime)")
     ap.add_argument("--dbg-pair-only", action="store_true", help="run the --dbg flags on the pair kernel only")
     ap.add_argument("--diag-sets", type=int, default=0, help="epi_sets used by the diagnosis stage (0 = automatic)")
+    ap.add_argument("--buckets", type=int, default=0, help="n_buckets of the searches (0 = bench default)")
     ap.add_argument("--exp", action="store_true", help="load liblmi_b200_exp.so (-DLMI_EXPERIMENTS build: dbg_flags honoured)")
     a = ap.parse_args()
     if a.exp:
@@ -91,7 +92,7 @@ def main():
             return
     import torch
     import bench
-    sys.argv = [sys.argv[0], "--rows", str(a.rows)]
+    sys.argv = [sys.argv[0], "--rows", str(a.rows)] + (["--buckets", str(a.buckets)] if a.buckets else [])
     args = bench.parse_args()
     device = torch.device("cuda", 0)
     inp = bench.build_inputs(args, device)
@@ -112,7 +113,9 @@ def main():
         rescore, chunk, flags = cfg[:3]
         sets = cfg[3] if len(cfg) > 3 else 0
         order = cfg[4] if len(cfg) > 4 else 0
+        hint = cfg[5] if len(cfg) > 5 else 0
         li.set_option("item_order", order)
+        li.set_option("l2_hint", hint)
         li.set_option("rescore", rescore)
         li.set_option("chunk_objects", chunk)
         li.set_option("epi_sets", sets)
@@ -134,7 +137,7 @@ def main():
         dd = out[0].cpu().numpy()
         if ref is None:
             ref = (dd, ids)
-        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, item_order=order, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
+        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, item_order=order, l2_hint=hint, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
                          ms_per_search=ev0.elapsed_time(ev1) / a.steps, k3_ms_avg=st["ms_rescore_avg"],
                          k3_sm_mhz=st["k3_sm_mhz"], work_items=st["n_work_items"], pairs=st["pairs"],
                          padded_pairs=st["padded_pairs"], tile_efficiency=st["pairs"] / max(st["padded_pairs"], 1),

@@ -75,6 +75,7 @@ struct lmi_index {
   int timing = 1;
   int dbg_flags = 0;                        // kernel experiments; honoured by -DLMI_EXPERIMENTS builds only
   int item_order = 0;                       // CTA-pair kernel work list: 0 = full pairs first, then half pairs; 1 = bucket-major
+  int l2_hint = 0;                          // CTA-pair kernel: per-item L2 eviction priority on the chunk loads (option "l2_hint")
   int epi_sets = 0;                         // CTA-pair kernel: epilogue warp sets (0 = automatic: 2 while k' <= 32)
   int rank = 0, world = 1, policy = LMI_SHARD_BUCKETS;
 

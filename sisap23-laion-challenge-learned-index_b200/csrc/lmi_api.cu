@@ -146,6 +146,8 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   } else if (n == "kprime_extra") {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
     idx->kprime_extra = (int)value;
+  } else if (n == "l2_hint") {
+    idx->l2_hint = value ? 1 : 0;
   } else if (n == "item_order") {
     if (value < 0 || value > 2) return set_error(LMI_ERR_ARG, "item_order: 0 (full pairs first), 1 (bucket-major) or 2 (0 + three-tile buckets as three half pairs)");
     idx->item_order = (int)value;

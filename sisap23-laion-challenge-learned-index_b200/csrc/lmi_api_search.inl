@@ -114,7 +114,7 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
         if (e != cudaSuccess) return e;
         kern<<<idx->num_sms & ~1, threads, smem, st>>>(idx->tmap_x32, idx->tmap_x3_32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                        idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                       idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), stage_box, dbg);
+                                                       idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), stage_box | (idx->l2_hint ? 2 : 0), dbg);
         return cudaSuccess;
       };
       // 16 KB stages per CTA (half tiles) beside SETS x [k' + 16][128] x 8 B candidate lists.  Two epilogue warp

@@ -179,21 +179,25 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
         for (long long c = 0; c < ch; ++c)
           for (long long t = 0; t < qt; ++t) {
             const long long r0 = t * kTileQ, r = min((long long)kTileQ, m - r0), h = (r + 1) / 2;
-            emit_rows(it_half, c, r0, h, kItemShared | kItemHalf);
-            emit_rows(it_half, c, r0 + h, r - h, kItemShared | kItemHalf);
+            const int lastf = (t == qt - 1) ? kItemLastReader : 0;          // the three run at one speed and share the chunk
+            emit_rows(it_half, c, r0, h, kItemShared | kItemHalf | lastf);
+            emit_rows(it_half, c, r0 + h, r - h, kItemShared | kItemHalf | lastf);
           }
       } else if (pair_mode) {
         for (long long c = 0; c < ch; ++c)
           for (long long p = 0; p < pairs_per_chunk; ++p) {
             const long long r0 = 2 * p * kTileQ;
             if (2 * p + 1 < qt) {
-              emit_rows(it, c, r0, kTileQ, kItemShared);
-              emit_rows(it, c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared);
+              // kItemLastReader: the last full pair of a chunk (the earlier ones run at the same speed just ahead of it and
+              // leave the chunk in L2; nothing that could still find it there comes after)
+              const int lastf = (p == qt / 2 - 1) ? kItemLastReader : 0;
+              emit_rows(it, c, r0, kTileQ, kItemShared | lastf);
+              emit_rows(it, c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared | lastf);
             } else {                                           // odd last tile: two halves (the second may be empty)
               const long long r = m - r0, h = (r + 1) / 2;
-              long long& ih = split_order ? it_half : it;
-              emit_rows(ih, c, r0, h, kItemShared | kItemHalf);
-              emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf);
+              long long& ih = split_order ? it_half : it;      // (runs at twice the speed of the full pairs: shares nothing)
+              emit_rows(ih, c, r0, h, kItemShared | kItemHalf | kItemLastReader);
+              emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf | kItemLastReader);
             }
           }
       } else {

@@ -119,7 +119,7 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
                    const WorkItem* __restrict__ items, PlanScalars* __restrict__ sc,
                    uint32_t* __restrict__ qthr,                     // [nq] shared per-query threshold
                    Cand* __restrict__ plists,
-                   int stage_box,                                   // 1: one 3-D TMA box fills a stage (d % 256 == 0)
+                   int stage_box,                                   // bit 0: one 3-D TMA box fills a stage (d % 256 == 0); bit 1: L2 eviction hints per item
                    int dbg_flags) {                                 // experiments (LMI_EXPERIMENTS builds only)
   static_assert(SETS == 1 || SETS == 2, "one or two epilogue warp sets");
   static_assert(STAGES >= 4, "the issuer warps' phase tracking needs a ring longer than one tile (3 stages at d = 768)");
@@ -193,6 +193,10 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
       const uint32_t full_leader = ptx::mapa(ptx::smem_u32(full_bar), 0);
       int stage = 0; uint32_t phase = 0;
       int islot = 0; uint32_t iphase = 0;
+      // L2 eviction priority per item (option "l2_hint"): a chunk's last (or only) reader loads with evict_first, so the
+      // streams nobody will read again do not push the chunks that a second, equal-speed reader is about to re-read out of L2
+      const uint64_t pol_first = ptx::l2_policy_evict_first(), pol_normal = ptx::l2_policy_evict_normal();
+      const bool l2_hint = (stage_box & 2) != 0;
       for (;;) {
         int pr;
         if (crank == 0) {
@@ -228,7 +232,8 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
             const uint32_t sb = ptx::smem_u32(stage_base + (size_t)stage * kT2StageBytes);
             if (crank == 0) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&full_bar[stage]), (uint32_t)(2 * atoms * kT2AtomBytes));
             const uint32_t fb = full_leader + (uint32_t)stage * 8u;
-            if (stage_box) ptx::tma_load_3d_cg2(sb, &tmap_x3h, fb, 0, obj0, ks * kTsAtomsPerStage);
+            if ((stage_box & 1) && l2_hint) ptx::tma_load_3d_cg2_hint(sb, &tmap_x3h, fb, 0, obj0, ks * kTsAtomsPerStage, (wi.flags & kItemLastReader) ? pol_first : pol_normal);
+            else if (stage_box & 1) ptx::tma_load_3d_cg2(sb, &tmap_x3h, fb, 0, obj0, ks * kTsAtomsPerStage);
             else
               for (int a = 0; a < atoms; ++a)
                 ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
