@@ -94,6 +94,26 @@ def test_pair_kernel_equals_default_kernel(case, nb, k, chunk, sets):
         assert (a_ == a3).all() and (d_ == d3).all()
 
 
+@pytest.mark.parametrize("order,hint", [(1, 0), (2, 0), (0, 1), (2, 1)], ids=["bucket_major", "three_halves", "l2_hint", "three_halves_l2_hint"])
+@pytest.mark.parametrize("nb,k,chunk", [(4, 10, 0), (24, 10, 256), (48, 10, 512)])   # 600 queries x nb / 48 buckets: ~1, ~3 and ~5 query tiles per bucket
+def test_pair_kernel_work_list_variants(case, nb, k, chunk, order, hint):
+    """Work-list orders of the CTA-pair kernel (option "item_order": 0 full pairs first -- the default --, 1 bucket-major,
+    2 three-tile buckets as three half pairs) and the L2 eviction hint on the chunk loads (option "l2_hint") change when
+    and how a chunk is streamed, never what is scored: ids and distances equal the default's bit for bit."""
+    c = case
+    ref = _index(c, PAIR, chunk_objects=chunk)
+    d0, a0 = _search(ref, c, nb, k)
+    li = _index(c, PAIR, chunk_objects=chunk)
+    li.set_option("item_order", order)
+    li.set_option("l2_hint", hint)
+    for _ in range(2):
+        d, a = _search(li, c, nb, k)
+        assert li.stats()["rescore_kernel"] == "rescore_ts2_kernel"
+        assert (a == a0).all() and (d == d0).all()
+    if order == 2:
+        assert li.stats()["n_work_items"] >= ref.stats()["n_work_items"]
+
+
 def test_pair_kernel_search_single(case):
     c = case
     li3, li1 = _index(c, PAIR), _index(c, 1)
