@@ -85,7 +85,8 @@ void lmi_destroy(lmi_index* idx);
 /* name/value tunables: "rescore" (LMI_RESCORE_*), "chunk_objects" (0 = chosen per search), "kprime_extra",
  * "epi_sets" (CTA-pair kernel: epilogue warp sets, 0 = automatic), "item_order" (CTA-pair work list: 0 = full pairs
  * first, 1 = bucket-major, 2 = experiment: 0 + three-tile buckets as three half pairs), "l2_hint" (CTA-pair kernel,
- * experiment: 1 = a chunk's last reader loads with L2 evict_first), "timing" (1 = record per-stage CUDA events). */
+ * experiment: 1 = a chunk's last reader loads with L2 evict_first), "lockstep" (CTA-pair kernel, experiment: 1 = a half
+ * pair follows its chunk's full pair tile by tile; measured slower, default 0), "timing" (1 = record per-stage CUDA events). */
 int lmi_set_option(lmi_index* idx, const char* name, int64_t value);
 
 /* multi-GPU: this index holds shard `rank` of `world`.  Call before lmi_store_begin. */

@@ -114,6 +114,8 @@ def main():
         sets = cfg[3] if len(cfg) > 3 else 0
         order = cfg[4] if len(cfg) > 4 else 0
         hint = cfg[5] if len(cfg) > 5 else 0
+        lock = cfg[6] if len(cfg) > 6 else 0
+        li.set_option("lockstep", lock)
         li.set_option("item_order", order)
         li.set_option("l2_hint", hint)
         li.set_option("rescore", rescore)
@@ -137,7 +139,7 @@ def main():
         dd = out[0].cpu().numpy()
         if ref is None:
             ref = (dd, ids)
-        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, item_order=order, l2_hint=hint, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
+        runs.append(dict(rescore=rescore, dbg_flags=flags, epi_sets=sets, item_order=order, l2_hint=hint, lockstep=lock, kernel=st["rescore_kernel"], chunk_objects=st["chunk_objects"],
                          ms_per_search=ev0.elapsed_time(ev1) / a.steps, k3_ms_avg=st["ms_rescore_avg"],
                          k3_sm_mhz=st["k3_sm_mhz"], work_items=st["n_work_items"], pairs=st["pairs"],
                          padded_pairs=st["padded_pairs"], tile_efficiency=st["pairs"] / max(st["padded_pairs"], 1),

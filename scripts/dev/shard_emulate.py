@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--rows", type=int, default=10_000_000)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--item-orders", default="0", help="comma list of item_order values (0 = full pairs first, 1 = bucket-major)")
+    ap.add_argument("--locksteps", default="0", help="comma list of lockstep values (0 off, 1 on) tried for every order")
     ap.add_argument("--merge", action="store_true", help="also build every rank's shard, concatenate the partials (the all-gather) "
                                                          "and time merge_partials_kernel")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "shard_emulate.json"))
@@ -47,9 +48,12 @@ def main():
             li.set_model(inp["weights"], inp["biases"])
             li.prepare_device(inp["data_f16"], inp["pred_categories"])
             part = torch.empty(li.partial_bytes(nq, k), dtype=torch.uint8, device=dev)
-            for chunk, order in [(int(c), int(o)) for c in a.chunks.split(",") for o in a.item_orders.split(",")]:
+            ref_part = None
+            for chunk, order, lock in [(int(c), int(o), int(l)) for c in a.chunks.split(",") for o in a.item_orders.split(",")
+                                       for l in a.locksteps.split(",")]:
                 li.set_option("chunk_objects", chunk)
                 li.set_option("item_order", order)
+                li.set_option("lockstep", lock)
                 for _ in range(3):
                     li.search_partial_device(qn, qs, nb, k, part)
                 torch.cuda.synchronize(); li.stats()
@@ -59,7 +63,11 @@ def main():
                     li.search_partial_device(qn, qs, nb, k, part)
                 e1.record(); torch.cuda.synchronize()
                 st = li.stats()
-                runs.append(dict(world=world, rank=rank, policy=a.policy, k=k, item_order=order, chunk_objects=st["chunk_objects"],
+                if ref_part is None:
+                    ref_part = part.clone()
+                same = bool(torch.equal(ref_part, part))
+                runs.append(dict(world=world, rank=rank, policy=a.policy, k=k, item_order=order, lockstep=lock, partial_equal_to_first=same,
+                                 chunk_objects=st["chunk_objects"],
                                  ms_partial_search=e0.elapsed_time(e1) / a.steps, ms_navigate=st["ms_navigate"], ms_plan=st["ms_plan"],
                                  ms_rescore_avg=st["ms_rescore_avg"], ms_finalize=st["ms_finalize"], kernel=st["rescore_kernel"],
                                  work_items=st["n_work_items"], partial_lists=st["n_partial_lists"], pairs=st["pairs"],

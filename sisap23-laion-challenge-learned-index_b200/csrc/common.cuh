@@ -37,6 +37,8 @@ struct __align__(16) WorkItem {
 constexpr int kItemShared = 1;
 constexpr int kItemHalf = 2;      // CTA-pair kernel: half tile (<= 64 rows per CTA), scored with M = 128 pair MMAs
 constexpr int kItemLastReader = 4; // CTA-pair kernel: no later work item streams this object chunk (its loads may leave L2 first)
+constexpr int kItemLeads = 8;       // CTA-pair kernel, lock-step option: the NEXT pair of the list streams the same chunk twice as fast; publish progress
+constexpr int kItemFollows = 16;    //   ... this pair follows the previous one (same chunk): it loads a tile only once the leader has asked for it
 
 struct __align__(8) Cand {  // entry of a partial top-k' list
   float score;              // dot(q, x) * inv_norm(x)  (cosine times |q|)

@@ -76,6 +76,8 @@ struct lmi_index {
   int dbg_flags = 0;                        // kernel experiments; honoured by -DLMI_EXPERIMENTS builds only
   int item_order = 0;                       // CTA-pair kernel work list: 0 = full pairs first, then half pairs; 1 = bucket-major
   int l2_hint = 0;                          // CTA-pair kernel: per-item L2 eviction priority on the chunk loads (option "l2_hint")
+  int lockstep = 0;                         // CTA-pair kernel: half pairs follow their chunk's full pair in lock-step (option "lockstep": 0 off, 1 on, -1 on shards)
+  bool lockstep_now = false;
   int epi_sets = 0;                         // CTA-pair kernel: epilogue warp sets (0 = automatic: 2 while k' <= 32)
   int rank = 0, world = 1, policy = LMI_SHARD_BUCKETS;
 
@@ -113,7 +115,7 @@ struct lmi_index {
   // search workspace (grow-only)
   lmi::DevBuf ws_qnav, ws_q16, ws_out_d, ws_out_i, ws_thr, ws_cls64;
   lmi::PinBuf pin_in, pin_out;               // staging for pageable caller buffers (lmi_search / lmi_search_rank)
-  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr, uncert;
+  lmi::DevBuf top_cls, m_b, qoff, chunks_b, plist_base, slot_pair, pair_slot, items, plists, qg, scalars, qthr, uncert, progress;
   lmi::DevBuf nav_cls, nav_probs, nav_x;
   CUtensorMap tmap_q{};
   void* tmap_q_ptr = nullptr; size_t tmap_q_rows = 0;

@@ -146,6 +146,9 @@ int lmi_set_option(lmi_index* idx, const char* name, int64_t value) {
   } else if (n == "kprime_extra") {
     if (value < 0 || value > 64) return set_error(LMI_ERR_ARG, "kprime_extra out of range");
     idx->kprime_extra = (int)value;
+  } else if (n == "lockstep") {
+    if (value < -1 || value > 1) return set_error(LMI_ERR_ARG, "lockstep: 0 (off), 1 (on) or -1 (on when the index is a shard)");
+    idx->lockstep = (int)value;
   } else if (n == "l2_hint") {
     idx->l2_hint = value ? 1 : 0;
   } else if (n == "item_order") {

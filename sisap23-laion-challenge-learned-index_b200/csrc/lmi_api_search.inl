@@ -114,7 +114,8 @@ static int launch_rescore(lmi_index* idx, const uint16_t* q16_dev, int nb, cudaS
         if (e != cudaSuccess) return e;
         kern<<<idx->num_sms & ~1, threads, smem, st>>>(idx->tmap_x32, idx->tmap_x3_32, q16_dev, idx->slot_pair.as<int32_t>(), nb, d, idx->inv_norm,
                                                        idx->items.as<WorkItem>(), idx->scalars.as<PlanScalars>(),
-                                                       idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(), stage_box | (idx->l2_hint ? 2 : 0), dbg);
+                                                       idx->qthr.as<uint32_t>(), idx->plists.as<Cand>(),
+                                                       stage_box | (idx->l2_hint ? 2 : 0) | (idx->lockstep_now ? 4 : 0), dbg, idx->progress.as<int32_t>());
         return cudaSuccess;
       };
       // 16 KB stages per CTA (half tiles) beside SETS x [k' + 16][128] x 8 B candidate lists.  Two epilogue warp
@@ -229,6 +230,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   const int64_t max_items = std::max<int64_t>(1, std::min(items_a, items_b));
   if (max_items >= (1LL << 31)) return set_error(LMI_ERR_NOMEM, "work list too large; raise chunk_objects");
   LMI_CUDA(idx->items.reserve((size_t)max_items * sizeof(WorkItem)));
+  LMI_CUDA(idx->progress.reserve((size_t)(max_items / 2 + 2) * sizeof(int32_t)));
   const int64_t max_plists = std::max<int64_t>(1, nq * top_nb_chunks);
   LMI_CUDA(idx->plists.reserve((size_t)max_plists * KP * sizeof(Cand)));
   // an empty shard has no tensor map and no work items: the (idle) CUDA-core kernel is launched instead
@@ -239,6 +241,9 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
     else if (KP <= 64) kernel = LMI_RESCORE_TC_SS;
   }
   idx->kernel_now = kernel;
+  // lock-step followers (option "lockstep": 1 on, 0 off, -1 automatic = on a sharded index) need the bucket-major list
+  idx->lockstep_now = kernel == LMI_RESCORE_TC_PAIR && (idx->lockstep == 1 || (idx->lockstep < 0 && idx->world > 1));
+  if (idx->lockstep_now) LMI_CUDA(cudaMemsetAsync(idx->progress.p, 0, (size_t)(max_items / 2 + 2) * sizeof(int32_t), st));
   const bool use_tc = (kernel == LMI_RESCORE_TC_SS);       // SS kernel: needs the bucket-ordered query copy
   if (kernel == LMI_RESCORE_TC || kernel == LMI_RESCORE_TC_PAIR) {
     LMI_CUDA(idx->qthr.reserve((size_t)nq * 4));
@@ -274,7 +279,7 @@ static int run_search(lmi_index* idx, const float* q_nav_dev, const int64_t* cls
   plan_build_kernel<<<1, 1024, 0, st>>>(idx->m_b.as<int32_t>(), idx->bucket_ptr.as<int64_t>(), C, chunk,
                                         idx->qoff.as<int32_t>(), idx->chunks_b.as<int32_t>(), idx->plist_base.as<int64_t>(),
                                         idx->items.as<WorkItem>(), (int)max_items, idx->scalars.as<PlanScalars>(),
-                                        kernel == LMI_RESCORE_TC_PAIR ? (idx->item_order == 1 ? 2 : idx->item_order == 2 ? 3 : 1) : 0);
+                                        kernel == LMI_RESCORE_TC_PAIR ? ((idx->item_order == 1 || idx->lockstep_now) ? 2 : idx->item_order == 2 ? 3 : 1) : 0);
   plan_scatter_kernel<<<C, kScatterThreads, 0, st>>>(top, n_pairs, C, idx->qoff.as<int32_t>(), idx->bucket_ptr.as<int64_t>(),
                                          idx->slot_pair.as<int32_t>(), idx->pair_slot.as<int32_t>());
   plan_mark_invalid_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(top, n_pairs, C, idx->pair_slot.as<int32_t>());

@@ -190,14 +190,16 @@ plan_build_kernel(const int32_t* __restrict__ m_b, const int64_t* __restrict__ b
             if (2 * p + 1 < qt) {
               // kItemLastReader: the last full pair of a chunk (the earlier ones run at the same speed just ahead of it and
               // leave the chunk in L2; nothing that could still find it there comes after)
-              const int lastf = (p == qt / 2 - 1) ? kItemLastReader : 0;
+              // bucket-major order: the half pair of an odd bucket is the next pair of the list (lock-step option of the kernel)
+              const int lastf = (p == qt / 2 - 1) ? (kItemLastReader | ((!split_order && (qt & 1)) ? kItemLeads : 0)) : 0;
               emit_rows(it, c, r0, kTileQ, kItemShared | lastf);
               emit_rows(it, c, r0 + kTileQ, min((long long)kTileQ, m - r0 - kTileQ), kItemShared | lastf);
             } else {                                           // odd last tile: two halves (the second may be empty)
               const long long r = m - r0, h = (r + 1) / 2;
-              long long& ih = split_order ? it_half : it;      // (runs at twice the speed of the full pairs: shares nothing)
-              emit_rows(ih, c, r0, h, kItemShared | kItemHalf | kItemLastReader);
-              emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf | kItemLastReader);
+              long long& ih = split_order ? it_half : it;      // (runs at twice the speed of the full pairs unless it follows in lock-step)
+              const int fol = (!split_order && qt >= 3) ? kItemFollows : 0;
+              emit_rows(ih, c, r0, h, kItemShared | kItemHalf | kItemLastReader | fol);
+              emit_rows(ih, c, r0 + h, r - h, kItemShared | kItemHalf | kItemLastReader | fol);
             }
           }
       } else {

@@ -119,8 +119,9 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
                    const WorkItem* __restrict__ items, PlanScalars* __restrict__ sc,
                    uint32_t* __restrict__ qthr,                     // [nq] shared per-query threshold
                    Cand* __restrict__ plists,
-                   int stage_box,                                   // bit 0: one 3-D TMA box fills a stage (d % 256 == 0); bit 1: L2 eviction hints per item
-                   int dbg_flags) {                                 // experiments (LMI_EXPERIMENTS builds only)
+                   int stage_box,                                   // bit 0: one 3-D TMA box fills a stage (d % 256 == 0); bit 1: L2 eviction hints per item; bit 2: lock-step followers
+                   int dbg_flags,                                   // experiments (LMI_EXPERIMENTS builds only)
+                   int32_t* __restrict__ progress) {                // [pairs] lock-step option (stage_box bit 2): tiles requested so far by a leading pair
   static_assert(SETS == 1 || SETS == 2, "one or two epilogue warp sets");
   static_assert(STAGES >= 4, "the issuer warps' phase tracking needs a ring longer than one tile (3 stages at d = 768)");
   static_assert(2 * STAGES * 8 + 9 * 8 + 4 * kTsItemRing * 4 + 16 <= 512, "barrier area too small");
@@ -197,6 +198,14 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
       // streams nobody will read again do not push the chunks that a second, equal-speed reader is about to re-read out of L2
       const uint64_t pol_first = ptx::l2_policy_evict_first(), pol_normal = ptx::l2_policy_evict_normal();
       const bool l2_hint = (stage_box & 2) != 0;
+      // Lock-step option: a half pair consumes its chunk twice as fast as the full pair listed just before it (same
+      // chunk), runs ahead of it and both read the chunk from DRAM.  As a FOLLOWER it asks for tile t only once the
+      // leader has asked for it, so its loads hit L2 (or merge with the leader's miss) and the chunk crosses the HBM
+      // interface once; it then runs at the leader's pace with its tensor pipe half idle -- a win where HBM, not the
+      // tensor pipe or the power cap, bounds the kernel (shards).  The counter is a timing hint, not a dependency: the
+      // leader never waits, and a follower that sees no progress for kLockSpins polls runs free for the rest of its item.
+      const bool lockstep = (stage_box & 4) != 0;
+      constexpr int kLockSpins = 64;
       for (;;) {
         int pr;
         if (crank == 0) {
@@ -216,7 +225,16 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
         if (pr >= n_pairs) break;
         const WorkItem wi = items[2 * pr];            // both entries of a pair score the same object chunk
         const int n_tiles = (wi.obj_count + kTsBlockN - 1) / kTsBlockN;
+        const bool leads = lockstep && (wi.flags & kItemLeads) && crank == 0;
+        bool follows = lockstep && (wi.flags & kItemFollows) && pr > 0;
+        volatile int32_t* lead_prog = progress + (follows ? pr - 1 : pr);
+        int lead_seen = 0;
         for (int t = 0; t < n_tiles; ++t) {
+          if (follows && lead_seen <= t) {
+            int spins = 0;
+            do { lead_seen = *lead_prog; } while (lead_seen <= t && ++spins < kLockSpins);
+            if (lead_seen <= t) follows = false;
+          }
           int obj0 = wi.obj_begin + t * kTsBlockN + (int)crank * kT2HalfN;
           // experiment 256: half-pair items re-read a 16-tile window (always an L2 hit) instead of streaming their chunk a
           // second time -- isolates what the second reader's DRAM traffic costs (results invalid)
@@ -239,6 +257,7 @@ rescore_ts2_kernel(const __grid_constant__ CUtensorMap tmap_xh,     // bucket st
                 ptx::tma_load_2d_cg2(sb + a * kT2AtomBytes, &tmap_xh, fb, (ks * kTsAtomsPerStage + a) * kTsAtomK, obj0);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
+          if (leads) *lead_prog = (t + 1 == n_tiles) ? 0x7fffffff : t + 1;
         }
       }
       // Producer tail: no CTA exits while commit arrivals for its stages may still be in flight

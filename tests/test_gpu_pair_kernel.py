@@ -94,18 +94,20 @@ def test_pair_kernel_equals_default_kernel(case, nb, k, chunk, sets):
         assert (a_ == a3).all() and (d_ == d3).all()
 
 
-@pytest.mark.parametrize("order,hint", [(1, 0), (2, 0), (0, 1), (2, 1)], ids=["bucket_major", "three_halves", "l2_hint", "three_halves_l2_hint"])
+@pytest.mark.parametrize("order,hint", [(1, 0), (2, 0), (0, 1), (2, 1), (0, 2)],
+                         ids=["bucket_major", "three_halves", "l2_hint", "three_halves_l2_hint", "lockstep"])
 @pytest.mark.parametrize("nb,k,chunk", [(4, 10, 0), (24, 10, 256), (48, 10, 512)])   # 600 queries x nb / 48 buckets: ~1, ~3 and ~5 query tiles per bucket
 def test_pair_kernel_work_list_variants(case, nb, k, chunk, order, hint):
     """Work-list orders of the CTA-pair kernel (option "item_order": 0 full pairs first -- the default --, 1 bucket-major,
-    2 three-tile buckets as three half pairs) and the L2 eviction hint on the chunk loads (option "l2_hint") change when
+    2 three-tile buckets as three half pairs) the L2 eviction hint on the chunk loads (option "l2_hint") and lock-step followers (option "lockstep") change when
     and how a chunk is streamed, never what is scored: ids and distances equal the default's bit for bit."""
     c = case
     ref = _index(c, PAIR, chunk_objects=chunk)
     d0, a0 = _search(ref, c, nb, k)
     li = _index(c, PAIR, chunk_objects=chunk)
     li.set_option("item_order", order)
-    li.set_option("l2_hint", hint)
+    li.set_option("l2_hint", hint & 1)
+    li.set_option("lockstep", hint >> 1)            # half pairs follow their chunk's full pair (bucket-major list)
     for _ in range(2):
         d, a = _search(li, c, nb, k)
         assert li.stats()["rescore_kernel"] == "rescore_ts2_kernel"
