@@ -151,6 +151,9 @@ class GpuLearnedIndex:
             if env_sets not in ("0", "1", "2"):
                 raise ValueError(f"LMI_EPI_SETS must be 0, 1 or 2, got {env_sets!r}")
             self.set_option("epi_sets", int(env_sets))
+        for item in filter(None, os.environ.get("LMI_OPTIONS", "").split(",")):      # development: "name=value,..." -> lmi_set_option
+            name, _, value = item.partition("=")
+            self.set_option(name.strip(), int(value))
         if world > 1:
             check(self._lib.lmi_set_shard(self._h, rank, world, shard_policy))
         self.rank, self.world = rank, world
