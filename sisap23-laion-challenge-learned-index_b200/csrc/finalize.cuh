@@ -319,7 +319,55 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
   double max_err = 0.0;
   // (the round-based selections leave the scores in descending order; read before they are overwritten)
   const float score_R = (n_sel == R) ? (sel_ne != 0 ? score_R_sel : (float)s_dist[warp][R - 1]) : 0.f;
+  const bool list_full = (n_sel == R);
   __syncwarp();
+  // Only candidates that can still reach the top k are re-scored.  With a_k the k-th largest fp32 cosine among the
+  // selected and eps the error bound of the certificate, an entry below a_k - 2 eps has a float64 cosine below
+  // a_k - eps, which the k entries at or above a_k all reach: it cannot be among the k best.  k' = 16 selected for
+  // k = 10 shrink to 10-11 rows read from HBM and re-scored (k' = 128 for k = 100 to ~101); the result is unchanged.
+  if (n_sel > k) {
+    constexpr int kPer = kSel / 32;                      // selected entries per lane
+    uint32_t key[kPer];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      const int t = lane + 32 * u;
+      key[u] = (t < n_sel) ? fin_key((float)s_dist[warp][t]) : 0u;
+    }
+    uint32_t T = 0u;                                     // k-th largest key: the largest T with count(key >= T) >= k
+    for (int bit = 31; bit >= 0; --bit) {
+      const uint32_t cand = T | (1u << bit);
+      int c = 0;
+#pragma unroll
+      for (int u = 0; u < kPer; ++u) c += (key[u] >= cand) ? 1 : 0;
+      c = __reduce_add_sync(0xffffffffu, c);
+      if (c >= k) T = cand;
+    }
+    const double cut = (double)fin_unkey(T) - 2.0 * kCertEpsPerDim * (double)d * qn;      // scores are cosine x |q|
+    int32_t e_pos[kPer]; uint32_t e_rank[kPer]; double e_sc[kPer]; bool e_keep[kPer];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      const int t = lane + 32 * u;
+      e_keep[u] = false; e_pos[u] = 0; e_rank[u] = 0u; e_sc[u] = 0.0;
+      if (t < n_sel) {
+        e_pos[u] = s_pos[warp][t]; e_rank[u] = s_rank[warp][t]; e_sc[u] = s_dist[warp][t];
+        e_keep[u] = e_sc[u] >= cut;
+      }
+    }
+    __syncwarp();
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    int out = 0;
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      const uint32_t m = __ballot_sync(0xffffffffu, e_keep[u]);
+      if (e_keep[u]) {
+        const int o = out + __popc(m & lt_mask);
+        s_pos[warp][o] = e_pos[u]; s_rank[warp][o] = e_rank[u]; s_dist[warp][o] = e_sc[u];
+      }
+      out += __popc(m);
+    }
+    __syncwarp();
+    n_sel = out;                                         // >= k: the k entries at or above a_k are kept
+  }
   const int grp = lane >> 3, sub = lane & 7;
   for (int t0 = 0; t0 < n_sel; t0 += 4) {
     const int t = t0 + grp;
@@ -375,7 +423,7 @@ finalize_kernel(int64_t nq, int nb, int k, int KP, int d,
     max_err = fmax(max_err, __shfl_xor_sync(0xffffffffu, max_err, o));
   }
   if (lane == 0) {
-    if (n_sel == R) {
+    if (list_full) {
       const double cos_dropped = (double)score_R / qn + kCertEpsPerDim * (double)d;
       const double cos_kth = 1.0 - kth_dist;     // kth_dist = 10000 if fewer than k results -> uncertified
       if (!(cos_dropped < cos_kth)) {
