@@ -64,6 +64,9 @@ def parse_args():
                    help="skip the e2e_dropin leg (GpuLearnedIndex.search with a host DataFrame: needs 2 x the dataset in host RAM)")
     p.add_argument("--nav-mode", choices=["sliced", "replicated"], default="sliced",
                    help="N > 1: every rank navigates 1/N of the batch + all-gather of the bucket lists, or all of it (no collective)")
+    p.add_argument("--nav-lookahead", type=int, default=0, choices=[0, 1],
+                   help="N > 1, pipelined: navigate the next batch's slice ahead of this batch's rescoring and gather its bucket "
+                        "lists on the exchange stream (no collective left on the search stream)")
     p.add_argument("--no-pipeline", action="store_true",
                    help="N > 1: issue every step's exchange on the search stream (no overlap with the next step's navigation)")
     p.add_argument("--dbg-flags", type=int, default=0, help="kernel experiments only; results are invalid when non-zero")
@@ -552,10 +555,11 @@ def run_b200(args):
     # (DistributedSearch.search_device_pipelined); every batch's merged result is complete inside the timed region
     # (flush before the closing event).  --no-pipeline issues everything on one stream.
     pipelined = world > 1 and not args.no_pipeline
+    lookahead = pipelined and args.nav_lookahead == 1 and args.nav_mode == "sliced"
 
     def step():
         if pipelined:
-            ds.search_device_pipelined(qn, qs, nb, k, out)
+            ds.search_device_pipelined(qn, qs, nb, k, out, next_q_nav=qn if lookahead else None)
         else:
             ds.search_device(qn, qs, nb, k, out)
 
@@ -821,7 +825,10 @@ def run_b200(args):
                        "shard": args.shard if world > 1 else "none", "rescore": args.rescore,
                        "navigation": args.nav_mode if world > 1 else "local",
                        "pipeline": ("exchange of batch i (all-gather + merge, side stream) overlaps navigation and planning "
-                                    "of batch i+1; all K merged results complete inside the timed region") if pipelined else "none",
+                                    "of batch i+1; all K merged results complete inside the timed region"
+                                    + ("; navigation look-ahead: batch i+1's slice is navigated before batch i's rescoring and its "
+                                       "bucket lists are gathered on the exchange stream (K navigations inside the region)" if lookahead else ""))
+                                   if pipelined else "none",
                        "synthetic": {"blobs": args.blobs, "sigma": args.sigma}},
             "e2e": e2e, "e2e_dropin": dropin, "gpu_launches": args.steps * (8 + (1 if world > 1 else 0)),   # nav, 4 plan kernels, rescoring, finalize, exact fallback (+ merge)
             "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,

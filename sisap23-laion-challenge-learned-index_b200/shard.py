@@ -124,6 +124,11 @@ class DistributedSearch:
         self._ring = None
         self._ring_done = [None, None]
         self._n_pipelined = 0
+        # navigation look-ahead (search_device_pipelined(next_q_nav=...)): two sets of list buffers, the prepared batch
+        self._la_bufs = None
+        self._la_read = [None, None]
+        self._la_n = 0
+        self._la_pending = None
 
     def search_device(self, q_nav_t, q_f16_t, n_buckets, k, out=None):
         import torch
@@ -146,7 +151,7 @@ class DistributedSearch:
         self.dist.all_gather_into_tensor(gathered, part, group=self.group)      # the exchange step of the search proper
         return self.li.merge_partials_device(gathered, self.world, nq, k, out)
 
-    def search_device_pipelined(self, q_nav_t, q_f16_t, n_buckets, k, out):
+    def search_device_pipelined(self, q_nav_t, q_f16_t, n_buckets, k, out, next_q_nav=None):
         """Throughput form of ``search_device`` for a stream of batches: the exchange step of batch i (all-gather of the
         partial results + merge kernel) runs on a side stream while the caller's stream goes on to batch i + 1, whose
         navigation, bucket-list all-gather and planning use the GPU only lightly.  Per-rank results, merge key and
@@ -157,7 +162,13 @@ class DistributedSearch:
         gathered buffers are double-buffered; a third call waits for the first one's exchange.  The exchange uses its
         own NCCL communicator (created collectively on the first call) so that it does not queue behind, or ahead of,
         the next batch's bucket-list all-gather on one NCCL stream.  Every rank must issue the same calls in the same
-        order, as with any collective."""
+        order, as with any collective.
+
+        ``next_q_nav`` (navigation look-ahead, sliced navigation only): the navigation vectors of the batch the NEXT call
+        will search.  This rank's slice of them goes through K1 now, ahead of this batch's rescoring, and the all-gather
+        of the bucket lists is queued on the exchange stream, where it runs beside this batch's finalize -- so the next
+        call finds its bucket lists ready and no collective is left on the search stream.  The next call must pass the
+        same tensor (same storage and shape) as its ``q_nav_t``; otherwise the prepared lists are ignored."""
         import torch
         nq = int(q_f16_t.shape[0])
         dev = q_f16_t.device
@@ -183,7 +194,16 @@ class DistributedSearch:
         if self._ring_done[slot] is not None:
             main.wait_event(self._ring_done[slot])           # the exchange two batches back has read `part`
         if self.slice_navigation:
-            every = self.navigate_sliced(q_nav_t, n_buckets)
+            key = (q_nav_t.data_ptr(), tuple(q_nav_t.shape), int(n_buckets))
+            la = self._la_pending
+            if la is not None and la[0] == key:
+                every = la[1]
+                main.wait_event(la[2])                       # bucket lists gathered on the exchange stream a batch ago
+            else:
+                every = self.navigate_sliced(q_nav_t, n_buckets)
+            self._la_pending = None
+            if next_q_nav is not None:
+                self._la_pending = self._navigate_ahead(next_q_nav, n_buckets, main)
             self.li.search_partial_classes_device(every, q_f16_t, n_buckets, k, part)
         else:
             self.li.search_partial_device(q_nav_t, q_f16_t, n_buckets, k, part)
@@ -197,6 +217,34 @@ class DistributedSearch:
             done.record(self._xs)
         self._ring_done[slot] = done
         return done
+
+    def _navigate_ahead(self, q_nav_t, n_buckets, main):
+        """K1 on this rank's slice of a FUTURE batch on the search stream, all-gather of the lists on the exchange
+        stream.  -> (key, gathered lists, event recorded behind the all-gather)"""
+        import torch
+        nq, dev, W = int(q_nav_t.shape[0]), q_nav_t.device, self.world
+        r = self.dist.get_rank(self.group)
+        per, lo, hi = query_slice_of_rank(nq, r, W)
+        if self._la_bufs is None or self._la_bufs[0][0].shape != (per, n_buckets):
+            self._la_bufs = [(torch.full((per, n_buckets), -1, dtype=torch.int32, device=dev),
+                              torch.empty(W * per, n_buckets, dtype=torch.int32, device=dev)) for _ in range(2)]
+            self._la_read = [None, None]
+        slot = self._la_n & 1
+        self._la_n += 1
+        mine, every = self._la_bufs[slot]
+        if self._la_read[slot] is not None:
+            main.wait_event(self._la_read[slot])             # the all-gather that last read `mine` has finished
+        if hi > lo:
+            self.li.navigate_device(q_nav_t[lo:hi], n_buckets, mine)
+        nav_done = torch.cuda.Event()
+        nav_done.record(main)
+        gathered = torch.cuda.Event()
+        with torch.cuda.stream(self._xs):
+            self._xs.wait_event(nav_done)
+            self.dist.all_gather_into_tensor(every, mine, group=self._xgroup)
+            gathered.record(self._xs)
+        self._la_read[slot] = gathered
+        return ((q_nav_t.data_ptr(), tuple(q_nav_t.shape), int(n_buckets)), every, gathered)
 
     def flush_pipelined(self):
         """The current stream waits for every exchange issued by ``search_device_pipelined``."""
